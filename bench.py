@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 wavefront path tracer (BASELINE.json metric:
+Mrays/s, all bounces, device-timed; workload C3 = configs[2]: procedural 1 007 232-triangle
+terrain+spheres scene, 1920x1080, 64 spp, depth 8 — the configuration north_star's target is
+quoted on; it fits one GPU).
+
+One step = one whole 64-spp frame through the hot path (raygen -> depth x (trace, shade)), film
+resident in HBM.  N>1 (torchrun, one rank per GPU): weak scaling — every rank renders its own
+disjoint 64-spp range [64*rank, 64*rank+64) of the same estimator and the partial films are summed
+onto rank 0 with one NCCL reduce per step, inside the timed region.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1..C5]
+
+--impl reference times the reference's own CPU implementation of the path on the host cores:
+the oracle's restated loop driving the real Embree 3.6.1 (oracle/_ref) where that was built,
+else the oracle port; each step is a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "smallpt-enoki-optix_b200")
+for p in (PKG, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+SEED = 0x5EED
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+def workload(name, scale=1.0):
+    import scenes
+    gen, W, H, spp, depth = scenes.CONFIGS[name]
+    return gen, W, H, spp, depth
+
+
+def alg_bytes(n_tris):
+    """Algorithmic bytes per ray segment (SURVEY §8d's formula with this layout):
+    one root->leaf descent of D = ceil(log8(T/3)) 80-byte nodes + one 3-triangle leaf of 48-byte blocks,
+    plus the SoA record streams each kernel must move."""
+    D = int(np.ceil(np.log(max(n_tris / 3.0, 8.0)) / np.log(8.0)))
+    trav = D * 80 + 3 * 48
+    trace = 32 + 16 + 4 + trav            # read (o,d) 2x16 B, write hit 16 B, prim id 4 B
+    shade = 40 + 16 + 48 + 40             # read ray 40 + hit 16 + attributes 48, write next ray 40
+    return dict(D=D, trav=trav, trace=trace, shade=shade, pipeline=trace + shade)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+def cpu_reference_run(sd, W, H, depth, spp, budget_s, threads=0):
+    """The oracle's restated loop (reference RNG: per-pixel PCG32) on Embree 3.6.1 when oracle/_ref
+    exists ("reference"), else on the oracle's own BVH ("port").  Returns (Mrays/s, segments, s, kind, cores)."""
+    import oracle_py as O
+    kind = "reference" if O.ref_available() else "port"
+    backend = "embree" if kind == "reference" else "bvh"
+    m = O.Mesh(sd.pos, sd.idx, sd.nrm, sd.nidx, sd.mat, sd.albedo)
+    c = sd.camera
+    cam = O.camera(c["look_from"], c["look_at"], c["up"], fov_y=c["fov_y"])
+    m.backend(backend)  # build the CPU BVH outside the timed region (the reference does not time commit either)
+    cores = O.lib().orc_num_threads() if threads <= 0 else threads
+    t0 = time.perf_counter()
+    film, seg = m.render(backend, cam, W, H, 0, spp, depth, rng_mode=O.RNG_PCG32, threads=threads)
+    dt = time.perf_counter() - t0
+    return seg / dt / 1e6, seg, dt, kind, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import scenes
+    gen, W, H, spp, depth = workload(args.workload)
+    sd = gen()
+    # bounded sample: the full frame at 1 spp per step (C3: ~5 M segments, seconds on 8 cores)
+    sample_spp = 1
+    times, segs = [], 0
+    kind, cores = "port", 1
+    for i in range(args.warmup + args.steps):
+        mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, sample_spp, 0)
+        if i >= args.warmup:
+            times.append(dt); segs += seg
+    tot = sum(times)
+    val = segs / tot / 1e6
+    sample = f"{args.workload} scene ({sd.n_tris} tris) {W}x{H}, depth {depth}, {sample_spp} spp per step (of {spp})"
+    line = {"impl": "reference", "metric": "Mrays/s (all bounces)", "value": val, "unit": "Mrays/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
+                       "spp": spp, "depth": depth, "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import scenes
+    import wpt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — libwpt has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    gen, W, H, spp, depth = workload(args.workload)
+    if args.spp:
+        spp = args.spp
+    sd = gen()
+    t0 = time.perf_counter()
+    scene = wpt.scene_from(sd, device=local)
+    commit_s = time.perf_counter() - t0
+    bst = scene.stats()
+    cam = wpt.camera_from(sd)
+    N = W * H
+    r = wpt.Renderer(scene, W, H, args.spp_per_pass)
+    r.set_tuning(args.variant, args.ctas_per_sm, 0)
+    film = torch.zeros(3, N, device="cuda")
+    spp_begin = rank * spp            # disjoint, decorrelated spp ranges (RNG keyed on the global index)
+
+    def step():
+        film.zero_()
+        r.render(cam, film, spp_begin, spp, depth, seed=SEED)
+        if world > 1:
+            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)      # one NCCL reduce of the partial films
+        wpt.film_scale(film, 1.0 / (spp * world))
+        return r.finish()
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    segs, launches = 0, 0
+    for _ in range(args.steps):
+        st = step()
+        segs += st["segments"]; launches += st["kernel_launches"] + 1
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms, float(segs)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+        ms, segs_all = float(tm[0]), float(ts[1])
+    else:
+        segs_all = float(segs)
+    value = segs_all / (ms * 1e-3) / 1e6
+
+    if args.quick:
+        if rank == 0:
+            print(json.dumps({"quick": True, "value": value, "unit": "Mrays/s", "ms_per_step": ms / args.steps,
+                              "n_gpus": world, "gpu_launches": launches, "clocks": clocks}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- e2e: same metric through the host-buffer entry point (film zero -> render -> scale -> D2H)
+    host_film = np.empty((3, N), np.float32)
+    r.render_host(cam, spp_begin, min(spp, 4), depth, seed=SEED, out=host_film)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e_t0 = time.perf_counter()
+    e_segs = 0
+    e_steps = max(1, min(args.steps, 3))
+    for _ in range(e_steps):
+        _, st = r.render_host(cam, spp_begin, spp, depth, seed=SEED, out=host_film)
+        e_segs += st["segments"]
+    e_dt = time.perf_counter() - e_t0
+    et = torch.tensor([e_dt, float(e_segs)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        em = et.clone(); dist.all_reduce(em, op=dist.ReduceOp.MAX)
+        es = et.clone(); dist.all_reduce(es, op=dist.ReduceOp.SUM)
+        e_dt, e_segs_all = float(em[0]), float(es[1])
+    else:
+        e_segs_all = float(e_segs)
+    e2e = {"value": e_segs_all / e_dt / 1e6, "unit": "Mrays/s",
+           "h2d_bytes_per_step": C.sizeof(wpt.Camera) + C.sizeof(wpt.RenderConfig),
+           "d2h_bytes_per_step": 3 * N * 4,
+           "what": "wpt_render_host: host camera/config in, film zero + full frame + 1/spp + D2H of the planar film"}
+
+    # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
+    roof = None
+    if rank == 0:
+        r.set_profile(True)
+        film.zero_()
+        r.render(cam, film, spp_begin, spp, depth, seed=SEED)
+        pst = r.finish()
+        r.set_profile(False)
+        ab = alg_bytes(sd.n_tris)
+        peak, which = measured_peak_gbs()
+        n_trace = pst["passes"] * depth
+        trace_s = pst["ms_trace"] * 1e-3
+        achieved = pst["segments"] * ab["trace"] / trace_s / 1e9
+        roof = {"bound": "hbm", "kernel": "trace_persistent", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "peak_source": which, "traffic": None,
+                "alg_bytes_per_ray": ab["trace"], "rays_per_launch": pst["segments"] / n_trace,
+                "avg_launch_ms": pst["ms_trace"] / n_trace, "launches": n_trace,
+                "trace_mrays_s": pst["segments"] / trace_s / 1e6,
+                "share_of_step": {"raygen": pst["ms_raygen"] / pst["ms_total"], "trace": pst["ms_trace"] / pst["ms_total"],
+                                  "shade": pst["ms_shade"] / pst["ms_total"]},
+                "pipeline": {"alg_bytes_per_ray": ab["pipeline"],
+                             "achieved": value / world * 1e6 * ab["pipeline"] / 1e9,
+                             "frac": value / world * 1e6 * ab["pipeline"] / 1e9 / peak},
+                "live_per_bounce": pst["live"][:depth]}
+
+    # ---- CPU baseline beside it (rank 0, N=1 only; bounded sample)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, 1, 0)
+        cpu = {"value": mr, "unit": "Mrays/s", "cores": cores, "kind": kind,
+               "sample": f"same scene/camera, {W}x{H}, depth {depth}, 1 spp of {spp} ({seg} segments, {dt:.1f} s)"}
+
+    if rank == 0:
+        line = {"metric": "Mrays/s (all bounces, device-timed)", "value": value, "unit": "Mrays/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
+                           "spp": spp, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
+                           "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
+                               N * args.spp_per_pass * 56 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
+                           "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
+                                   "build_ms": bst["build_ms"], "upload_ms": bst["upload_ms"]}},
+                "ms_per_frame": ms / args.steps, "segments_per_step": segs_all / args.steps,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+                "commit_s": commit_s}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's spp")
+    ap.add_argument("--spp-per-pass", type=int, default=4)
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours" and not args.quick:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

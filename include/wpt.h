@@ -1,0 +1,174 @@
+/*
+ * wpt.h — C ABI of libwpt.so, the B200-native replacement for the reference's per-sample /
+ * per-bounce hot path.  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ * Every entry point returns 0 on success or a WPT_E_* code; wpt_last_error() gives the text
+ * (thread-local).  Nothing throws across the ABI (the reference throws std::runtime_error from
+ * OPTIX_CHECK/CUDA_CHECK, src/accel/optix_backend.h:25-82 — the C++ shim in
+ * smallpt-enoki-optix_b200/src/wpt_shim.h re-raises our codes the same way).
+ *
+ * All file:line citations are relative to the reference tree (/root/reference).
+ *
+ * There is NO CPU fallback: every compute entry point needs a CUDA device and fails with
+ * WPT_E_CUDA otherwise.
+ */
+#ifndef WPT_H
+#define WPT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WPT_VERSION 100
+
+enum {
+    WPT_OK = 0,
+    WPT_E_INVALID = 1,  /* bad argument */
+    WPT_E_CUDA = 2,     /* CUDA runtime error (text in wpt_last_error) */
+    WPT_E_STATE = 3,    /* call order (e.g. intersect before commit) */
+    WPT_E_LIMIT = 4,    /* size limit exceeded (W*H > 2^24, BVH depth, ...) */
+    WPT_E_IO = 5
+};
+
+const char *wpt_last_error(void);
+int wpt_version(void);
+
+/* ------------------------------------------------------------------ scene
+ * Replaces Scene::add_triangle_mesh's device upload (src/main.cpp:288-310) and
+ * Scene::commit -> OptixBackend::init + set_triangles_soup (src/main.cpp:312-318,
+ * src/accel/optix_backend.h:178-186, 283-364).  Array shapes are exactly the reference's
+ * AoS-flattened host vectors (src/main.cpp:160-223):
+ *   positions f32[3*n_positions], position_triplets i32[3*n_triangles] (global face order ==
+ *   tri_id), normals f32[3*n_normals], normal_triplets i32[3*n_triangles],
+ *   material_id i32[n_triangles] (src/main.cpp:185), albedo f32[3*n_materials] (the constant
+ *   1x1 reflectance texture of each LambertBsdf, src/main.cpp:40-44,104-106).
+ * Deviation: normal_triplets == NULL, or a negative index in a face, makes that
+ * face use its geometric normal instead of the reference's out-of-bounds gather.
+ * material_id == NULL -> all 0; albedo == NULL -> one white material (src/main.cpp:234,244).
+ * Host arrays are copied at create; the caller may free them afterwards. */
+typedef struct wpt_scene wpt_scene;
+typedef struct {
+    const float   *positions;
+    const int32_t *position_triplets;
+    const float   *normals;
+    const int32_t *normal_triplets;
+    const int32_t *material_id;
+    const float   *albedo;
+    uint32_t n_positions, n_triangles, n_normals, n_materials;
+} wpt_mesh_desc;
+
+typedef struct {
+    uint32_t n_triangles, n_nodes, n_leaf_slots, max_depth;
+    double   sah_cost;      /* of the wide tree, c_node=1, c_tri=0.3, relative to root area */
+    double   build_ms, upload_ms;
+    uint64_t node_bytes, tri_bytes, attr_bytes;
+} wpt_bvh_stats;
+
+int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
+/* SAH BVH build on the host, flatten to 80-byte 8-wide quantised nodes + 48-byte triangle blocks,
+ * one upload to `device`. */
+int  wpt_scene_commit(wpt_scene *s, int device);
+int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
+void wpt_scene_destroy(wpt_scene *s);
+
+/* ------------------------------------------------------------------ closest-hit on ray streams
+ * Replaces OptixBackend::intersect's launch (src/accel/optix_backend.h:422-460) and the device
+ * programs src/wavefront_isect.cu:48-112.  Field-for-field mirror of struct Params
+ * (src/optixdata.h:11-29): eight DEVICE f32 streams, a bool mask of size n or 1 (size 1 =
+ * broadcast, wavefront_isect.cu:86; NULL = all live), four DEVICE result streams.
+ * tmin/tmax stream pointers may be NULL, in which case the scalars are used (the reference
+ * materialises two constant arrays per bounce, src/ray.h:20-26).
+ * Contract: tri_id = -1 on miss (wavefront_isect.cu:70); t,u,v written only on hit; lanes masked
+ * out are left untouched (wavefront_isect.cu:87); u,v are the weights of vertex 1 and 2
+ * (src/add_math.h:6); no culling; tmin < t <= tmax.  `stream` is a cudaStream_t (NULL = default
+ * stream).  Asynchronous. */
+typedef struct {
+    const float *ox, *oy, *oz, *dx, *dy, *dz;
+    const float *tmin, *tmax; /* optional streams */
+    float tmin_scalar, tmax_scalar;
+} wpt_ray_streams;
+typedef struct {
+    int32_t *tri_id;
+    float   *t, *u, *v;
+} wpt_hit_streams;
+
+int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
+                  uint32_t n, const wpt_hit_streams *hits, void *stream);
+/* Same, HOST buffers in and out (copies inside; synchronous). */
+int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
+                       uint32_t n, const wpt_hit_streams *hits);
+
+/* ------------------------------------------------------------------ camera (src/pinhole.h:7-72) */
+typedef struct {
+    float origin[3], x[3], y[3], z[3];
+    float film_size_y, focal_dist, fov_y, lens_radius;
+} wpt_camera;
+/* ThinlensCamera ctor, src/pinhole.h:9-25 (host scalar math there too). */
+int wpt_camera_init(wpt_camera *c, const float look_from[3], const float look_at[3], const float up[3],
+                    float lens_radius, float focal_dist, float fov_y, float film_size_y);
+
+/* ------------------------------------------------------------------ the sample / bounce loop
+ * Replaces src/main.cpp:385-426: per sample, camera ray (pinhole.h:27-56), then `depth` segments of
+ * intersect -> film += contrib on miss -> Lambert bounce about the interpolated shading normal.
+ * RNG: counter-based Philox4x32-10, counter = (pixel, global spp index, slot, 0), key = seed;
+ * slot 0 -> lens(2)+jitter(2), slot 1+j -> scatter(2) of bounce j.  Keying on the GLOBAL spp index
+ * makes a [spp_begin, spp_begin+spp_count) shard on another GPU a disjoint, decorrelated part of
+ * the same estimator. */
+typedef struct {
+    int32_t  width, height;
+    int32_t  spp_begin, spp_count, depth;
+    uint64_t seed;
+    float    tmin, tmax;       /* src/ray.h:16 defaults: 1e-3, 1e20 */
+} wpt_render_config;
+
+#define WPT_MAX_DEPTH 64
+typedef struct {
+    uint64_t segments;                    /* ray segments actually traced (device counted) */
+    uint64_t live[WPT_MAX_DEPTH];         /* rays entering bounce j, summed over passes */
+    uint32_t passes, kernel_launches;
+    float    ms_total, ms_raygen, ms_trace, ms_shade; /* CUDA-event times; per-kernel only if profile=1 */
+} wpt_stats;
+
+typedef struct wpt_renderer wpt_renderer;
+/* Owns the double-buffered ray/hit queues for width*height*spp_per_pass paths in flight, all
+ * allocated here: wpt_render allocates nothing. profile != 0 brackets every kernel with events. */
+int  wpt_renderer_create(const wpt_scene *s, int32_t width, int32_t height, int32_t spp_per_pass,
+                         wpt_renderer **out);
+void wpt_renderer_destroy(wpt_renderer *r);
+int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
+/* Tuning knobs (0 = default): which trace kernel, CTAs per SM, block size. */
+int  wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int sort_rays);
+
+/* Adds the UN-normalised sum of the requested samples into DEVICE planar film_r/g/b
+ * (pixel_index = y*W + x, src/main.cpp:379-381,407).  Asynchronous on `stream`; `stats` (optional,
+ * host) is filled by wpt_render_finish, which synchronises. */
+int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
+               float *film_r, float *film_g, float *film_b, void *stream);
+int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream);
+/* film *= 1/spp (src/main.cpp:429), device, async */
+int wpt_film_scale(float *film_r, float *film_g, float *film_b, uint32_t n, float scale, void *stream);
+/* Whole frame, HOST film out (zero -> render -> scale 1/spp_count -> D2H), src/main.cpp:369-439. */
+int wpt_render_host(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
+                    float *film_r, float *film_g, float *film_b, wpt_stats *stats);
+
+/* ------------------------------------------------------------------ per-function device entry points
+ * (parity tests of the fused kernels' pieces against the oracle; all DEVICE buffers) */
+/* camera rays for pixels [0,W*H) of one global sample index: o,d as 6 planar streams */
+int wpt_raygen(const wpt_camera *cam, int32_t width, int32_t height, int32_t spp_index, uint64_t seed,
+               float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, void *stream);
+/* one shading step on given hits (tri_id>=0 lanes): next origin/direction/weight, planar streams */
+int wpt_shade_step(const wpt_scene *s, uint32_t n, const float *o_xyz[3], const float *d_xyz[3],
+                   const int32_t *tri_id, const float *t, const float *u, const float *v,
+                   const float *s0, const float *s1, float *next_o[3], float *next_d[3], float *weight[3],
+                   void *stream);
+/* Philox4x32-10 on device: out[4*i..] = philox(ctr=(i, c1, c2, 0), key) */
+int wpt_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, void *stream);
+
+/* ------------------------------------------------------------------ output (src/fimage.h:33-58)
+ * PFM: "PF\nW H\n-1\n", rows bottom-up, interleaved RGB float32 LE.  HOST planar inputs. */
+int wpt_save_pfm(const char *path, const float *r, const float *g, const float *b, uint32_t width,
+                 uint32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

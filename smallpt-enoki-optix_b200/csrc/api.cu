@@ -1,0 +1,560 @@
+// api.cu — the C ABI of libwpt.so (include/wpt.h).  Host C++; owns device memory, never throws.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/wpt.h"
+#include "bvh_build.h"
+#include "kernels.cuh"
+
+using namespace wpt;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg)
+{
+    g_err = msg;
+    return code;
+}
+#define WPT_CUDA(call)                                                                              \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return fail(WPT_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
+    } while (0)
+
+extern "C" const char *wpt_last_error(void) { return g_err.c_str(); }
+extern "C" int wpt_version(void) { return WPT_VERSION; }
+
+// ------------------------------------------------------------------------------------------------
+struct wpt_scene {
+    // host copies (src/main.cpp:296-309 keeps them in Enoki arrays)
+    std::vector<float> pos, nrm, albedo;
+    std::vector<int32_t> pidx, nidx, mat;
+    uint32_t n_tris = 0;
+    // device
+    int device = -1, num_sms = 0;
+    bool committed = false;
+    Node8 *d_nodes = nullptr;
+    Tri48 *d_tris = nullptr;
+    int32_t *d_prim = nullptr;
+    TriAttr48 *d_attr = nullptr;
+    float *d_albedo = nullptr;
+    uint32_t *d_cursor = nullptr;   // scratch cursor for wpt_intersect
+    BvhView view{};
+    wpt_bvh_stats stats{};
+};
+
+extern "C" int wpt_scene_create(const wpt_mesh_desc *m, wpt_scene **out)
+{
+    if (!m || !out) return fail(WPT_E_INVALID, "wpt_scene_create: null argument");
+    if (!m->positions || !m->position_triplets || m->n_triangles == 0 || m->n_positions == 0)
+        return fail(WPT_E_INVALID, "wpt_scene_create: positions/position_triplets required, n_triangles > 0");
+    if (m->n_triangles > 0x7fffffffu / 3) return fail(WPT_E_LIMIT, "wpt_scene_create: too many triangles");
+    wpt_scene *s = new (std::nothrow) wpt_scene();
+    if (!s) return fail(WPT_E_INVALID, "out of host memory");
+    s->n_tris = m->n_triangles;
+    s->pos.assign(m->positions, m->positions + 3 * (size_t)m->n_positions);
+    s->pidx.assign(m->position_triplets, m->position_triplets + 3 * (size_t)m->n_triangles);
+    if (m->normals && m->normal_triplets && m->n_normals) {
+        s->nrm.assign(m->normals, m->normals + 3 * (size_t)m->n_normals);
+        s->nidx.assign(m->normal_triplets, m->normal_triplets + 3 * (size_t)m->n_triangles);
+        for (int32_t v : s->nidx)
+            if (v >= (int32_t)m->n_normals) { delete s; return fail(WPT_E_INVALID, "normal index out of range"); }
+    }
+    if (m->albedo && m->n_materials) s->albedo.assign(m->albedo, m->albedo + 3 * (size_t)m->n_materials);
+    else s->albedo.assign(3, 1.0f);   // src/main.cpp:234: default material Spectrum(1.0)
+    const int32_t n_mat = (int32_t)(s->albedo.size() / 3);
+    if (m->material_id) {
+        s->mat.assign(m->material_id, m->material_id + m->n_triangles);
+        for (int32_t v : s->mat)
+            if (v < 0 || v >= n_mat) { delete s; return fail(WPT_E_INVALID, "material id out of range"); }
+    } else {
+        s->mat.assign(m->n_triangles, 0);
+    }
+    *out = s;
+    return WPT_OK;
+}
+
+static void scene_free_device(wpt_scene *s)
+{
+    if (s->device >= 0) cudaSetDevice(s->device);
+    cudaFree(s->d_nodes); cudaFree(s->d_tris); cudaFree(s->d_prim); cudaFree(s->d_attr);
+    cudaFree(s->d_albedo); cudaFree(s->d_cursor);
+    s->d_nodes = nullptr; s->d_tris = nullptr; s->d_prim = nullptr; s->d_attr = nullptr;
+    s->d_albedo = nullptr; s->d_cursor = nullptr;
+    s->committed = false;
+}
+
+extern "C" void wpt_scene_destroy(wpt_scene *s)
+{
+    if (!s) return;
+    scene_free_device(s);
+    delete s;
+}
+
+extern "C" int wpt_scene_commit(wpt_scene *s, int device)
+{
+    if (!s) return fail(WPT_E_INVALID, "wpt_scene_commit: null scene");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(WPT_E_CUDA, "wpt_scene_commit: no CUDA device (libwpt has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(WPT_E_INVALID, "wpt_scene_commit: bad device index");
+    if (s->committed) scene_free_device(s);
+
+    BuiltBvh b;
+    const char *err = nullptr;
+    if (!build_bvh8(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
+        return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
+
+    // per-ORIGINAL-triangle shading attributes: 3 vertex normals + material, one 48 B gather per hit
+    std::vector<TriAttr48> attr(s->n_tris);
+    const bool has_n = !s->nidx.empty();
+    for (uint32_t t = 0; t < s->n_tris; t++) {
+        TriAttr48 &a = attr[t];
+        bool ok = has_n;
+        if (ok) for (int k = 0; k < 3; k++) ok = ok && s->nidx[3 * t + k] >= 0;
+        if (ok) {
+            for (int k = 0; k < 3; k++) {
+                a.n0[k] = s->nrm[3 * (size_t)s->nidx[3 * t + 0] + k];
+                a.n1[k] = s->nrm[3 * (size_t)s->nidx[3 * t + 1] + k];
+                a.n2[k] = s->nrm[3 * (size_t)s->nidx[3 * t + 2] + k];
+            }
+        } else {
+            // documented deviation: geometric normal (src/add_math.h:9-16) instead of an OOB gather
+            const float *p0 = &s->pos[3 * (size_t)s->pidx[3 * t]], *p1 = &s->pos[3 * (size_t)s->pidx[3 * t + 1]],
+                        *p2 = &s->pos[3 * (size_t)s->pidx[3 * t + 2]];
+            const float e1[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]};
+            const float e2[3] = {p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2]};
+            float n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+            const float l = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            if (l > 0) { n[0] /= l; n[1] /= l; n[2] /= l; } else { n[0] = 0; n[1] = 1; n[2] = 0; }
+            for (int k = 0; k < 3; k++) a.n0[k] = a.n1[k] = a.n2[k] = n[k];
+        }
+        a.mat = s->mat[t];
+        a.pad[0] = a.pad[1] = 0;
+    }
+
+    const auto t0 = std::chrono::steady_clock::now();
+    WPT_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    WPT_CUDA(cudaGetDeviceProperties(&prop, device));
+    s->device = device;
+    s->num_sms = prop.multiProcessorCount;
+    WPT_CUDA(cudaMalloc(&s->d_nodes, b.nodes.size() * sizeof(Node8)));
+    WPT_CUDA(cudaMalloc(&s->d_tris, b.tris.size() * sizeof(Tri48)));
+    WPT_CUDA(cudaMalloc(&s->d_prim, b.prim_id.size() * sizeof(int32_t)));
+    WPT_CUDA(cudaMalloc(&s->d_attr, attr.size() * sizeof(TriAttr48)));
+    WPT_CUDA(cudaMalloc(&s->d_albedo, s->albedo.size() * sizeof(float)));
+    WPT_CUDA(cudaMalloc(&s->d_cursor, 64 * sizeof(uint32_t)));
+    WPT_CUDA(cudaMemcpy(s->d_nodes, b.nodes.data(), b.nodes.size() * sizeof(Node8), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_tris, b.tris.data(), b.tris.size() * sizeof(Tri48), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_prim, b.prim_id.data(), b.prim_id.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaDeviceSynchronize());
+    const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+
+    s->view.nodes = reinterpret_cast<const uint4 *>(s->d_nodes);
+    s->view.tris = reinterpret_cast<const float4 *>(s->d_tris);
+    s->view.prim_id = s->d_prim;
+    s->view.n_nodes = (uint32_t)b.nodes.size();
+    s->view.n_tris = (uint32_t)b.tris.size();
+    s->stats.n_triangles = s->n_tris;
+    s->stats.n_nodes = (uint32_t)b.nodes.size();
+    s->stats.n_leaf_slots = (uint32_t)b.tris.size();
+    s->stats.max_depth = b.max_depth;
+    s->stats.sah_cost = b.sah_cost;
+    s->stats.build_ms = b.build_ms;
+    s->stats.upload_ms = up_ms;
+    s->stats.node_bytes = b.nodes.size() * sizeof(Node8);
+    s->stats.tri_bytes = b.tris.size() * sizeof(Tri48) + b.prim_id.size() * sizeof(int32_t);
+    s->stats.attr_bytes = attr.size() * sizeof(TriAttr48);
+    s->committed = true;
+    return WPT_OK;
+}
+
+extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
+{
+    if (!s || !out) return fail(WPT_E_INVALID, "wpt_scene_stats: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_stats: scene not committed");
+    *out = s->stats;
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+static TraceTuning g_default_tune = {0, 0};
+
+extern "C" int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask,
+                             uint32_t mask_size, uint32_t n, const wpt_hit_streams *hits, void *stream)
+{
+    if (!s || !rays || !hits) return fail(WPT_E_INVALID, "wpt_intersect: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_intersect: scene not committed");
+    if (n == 0) return WPT_OK;
+    if (!rays->ox || !rays->oy || !rays->oz || !rays->dx || !rays->dy || !rays->dz || !hits->tri_id || !hits->t ||
+        !hits->u || !hits->v)
+        return fail(WPT_E_INVALID, "wpt_intersect: null stream");
+    if (mask && mask_size != 1 && mask_size != n) return fail(WPT_E_INVALID, "wpt_intersect: mask_size must be 1 or n");
+    cudaStream_t st = (cudaStream_t)stream;
+    WPT_CUDA(cudaSetDevice(s->device));
+    StreamIO io;
+    io.ox = rays->ox; io.oy = rays->oy; io.oz = rays->oz; io.dx = rays->dx; io.dy = rays->dy; io.dz = rays->dz;
+    io.tmin = rays->tmin; io.tmax = rays->tmax; io.tmin_s = rays->tmin_scalar; io.tmax_s = rays->tmax_scalar;
+    io.mask = mask; io.mask_size = mask_size;
+    io.tri_id = hits->tri_id; io.t = hits->t; io.u = hits->u; io.v = hits->v;
+    WPT_CUDA(cudaMemsetAsync(s->d_cursor, 0, sizeof(uint32_t), st));
+    launch_trace_streams(s->view, io, n, s->d_cursor, s->num_sms, g_default_tune, st);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+extern "C" int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask,
+                                  uint32_t mask_size, uint32_t n, const wpt_hit_streams *hits)
+{
+    if (!s || !rays || !hits) return fail(WPT_E_INVALID, "wpt_intersect_host: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_intersect_host: scene not committed");
+    if (n == 0) return WPT_OK;
+    WPT_CUDA(cudaSetDevice(s->device));
+    const size_t fb = sizeof(float) * (size_t)n;
+    float *d = nullptr;          // 8 ray streams + 3 float result streams + 1 int stream
+    uint8_t *dm = nullptr;
+    WPT_CUDA(cudaMalloc(&d, fb * 12));
+    const float *src[8] = {rays->ox, rays->oy, rays->oz, rays->dx, rays->dy, rays->dz, rays->tmin, rays->tmax};
+    wpt_ray_streams dr = *rays;
+    const float **dst[8] = {&dr.ox, &dr.oy, &dr.oz, &dr.dx, &dr.dy, &dr.dz, &dr.tmin, &dr.tmax};
+    int rc = WPT_OK;
+    for (int k = 0; k < 8 && rc == WPT_OK; k++) {
+        if (!src[k]) { if (k < 6) rc = fail(WPT_E_INVALID, "wpt_intersect_host: null stream"); continue; }
+        if (cudaMemcpy(d + (size_t)k * n, src[k], fb, cudaMemcpyHostToDevice) != cudaSuccess) rc = fail(WPT_E_CUDA, "H2D copy failed");
+        *dst[k] = d + (size_t)k * n;
+    }
+    if (rc == WPT_OK && mask) {
+        const size_t mb = mask_size == 1 ? 1 : n;
+        if (cudaMalloc(&dm, mb) != cudaSuccess || cudaMemcpy(dm, mask, mb, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = fail(WPT_E_CUDA, "mask copy failed");
+    }
+    wpt_hit_streams dh;
+    dh.tri_id = reinterpret_cast<int32_t *>(d + (size_t)8 * n);
+    dh.t = d + (size_t)9 * n; dh.u = d + (size_t)10 * n; dh.v = d + (size_t)11 * n;
+    if (rc == WPT_OK) {
+        // lanes the kernel leaves untouched must keep the caller's values
+        cudaMemcpy(dh.tri_id, hits->tri_id, fb, cudaMemcpyHostToDevice);
+        cudaMemcpy(dh.t, hits->t, fb, cudaMemcpyHostToDevice);
+        cudaMemcpy(dh.u, hits->u, fb, cudaMemcpyHostToDevice);
+        cudaMemcpy(dh.v, hits->v, fb, cudaMemcpyHostToDevice);
+        rc = wpt_intersect(s, &dr, dm, mask_size, n, &dh, nullptr);
+    }
+    if (rc == WPT_OK) {
+        if (cudaMemcpy(hits->tri_id, dh.tri_id, fb, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(hits->t, dh.t, fb, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(hits->u, dh.u, fb, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(hits->v, dh.v, fb, cudaMemcpyDeviceToHost) != cudaSuccess)
+            rc = fail(WPT_E_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(cudaGetLastError()));
+    }
+    cudaFree(d);
+    cudaFree(dm);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ThinlensCamera ctor, src/pinhole.h:9-25
+extern "C" int wpt_camera_init(wpt_camera *c, const float from[3], const float at[3], const float up[3],
+                               float lens_radius, float focal_dist, float fov_y, float film_size_y)
+{
+    if (!c || !from || !at || !up) return fail(WPT_E_INVALID, "wpt_camera_init: null argument");
+    auto norm = [](const float a[3], float o[3]) {
+        const float d = std::fmaf(a[2], a[2], std::fmaf(a[1], a[1], a[0] * a[0]));
+        const float r = 1.0f / std::sqrt(d);
+        o[0] = a[0] * r; o[1] = a[1] * r; o[2] = a[2] * r;
+    };
+    auto cross = [](const float a[3], const float b[3], float o[3]) {
+        o[0] = std::fmaf(a[1], b[2], -(a[2] * b[1]));
+        o[1] = std::fmaf(a[2], b[0], -(a[0] * b[2]));
+        o[2] = std::fmaf(a[0], b[1], -(a[1] * b[0]));
+    };
+    const float d[3] = {at[0] - from[0], at[1] - from[1], at[2] - from[2]};
+    float t[3];
+    std::memcpy(c->origin, from, sizeof(float) * 3);
+    norm(d, c->z);
+    cross(up, c->z, t);
+    norm(t, c->x);
+    cross(c->z, c->x, t);
+    norm(t, c->y);
+    c->film_size_y = film_size_y; c->focal_dist = focal_dist; c->fov_y = fov_y; c->lens_radius = lens_radius;
+    for (int k = 0; k < 3; k++)
+        if (!std::isfinite(c->x[k]) || !std::isfinite(c->y[k]) || !std::isfinite(c->z[k]))
+            return fail(WPT_E_INVALID, "wpt_camera_init: degenerate look_from/look_at/up");
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// renderer: the sample/bounce loop (src/main.cpp:385-426) as a wavefront pipeline
+// ------------------------------------------------------------------------------------------------
+struct wpt_renderer {
+    const wpt_scene *scene = nullptr;
+    int W = 0, H = 0, spp_per_pass = 1;
+    uint32_t capacity = 0;            // paths in flight = W*H*spp_per_pass
+    RayQueue q[2]{};
+    int4 *hits = nullptr;
+    PassCounters *counters = nullptr; // one per pass slot, zeroed per pass
+    unsigned long long *live_acc = nullptr;   // [WPT_MAX_DEPTH]
+    float *film = nullptr;            // 3*W*H, used by wpt_render_host only
+    bool profile = false;
+    TraceTuning tune{0, 0};
+    // bookkeeping of the render in flight
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    std::vector<cudaEvent_t> prof_events;     // pairs around each kernel when profile is on
+    std::vector<int> prof_kind;               // 0 raygen, 1 trace, 2 shade
+    uint32_t passes = 0, launches = 0;
+    int depth_in_flight = 0;
+    bool in_flight = false;
+};
+
+extern "C" void wpt_renderer_destroy(wpt_renderer *r)
+{
+    if (!r) return;
+    if (r->scene && r->scene->device >= 0) cudaSetDevice(r->scene->device);
+    for (int k = 0; k < 2; k++) { cudaFree(r->q[k].a); cudaFree(r->q[k].b); cudaFree(r->q[k].c); }
+    cudaFree(r->hits); cudaFree(r->counters); cudaFree(r->live_acc); cudaFree(r->film);
+    if (r->ev_begin) cudaEventDestroy(r->ev_begin);
+    if (r->ev_end) cudaEventDestroy(r->ev_end);
+    for (cudaEvent_t e : r->prof_events) cudaEventDestroy(e);
+    delete r;
+}
+
+extern "C" int wpt_renderer_create(const wpt_scene *s, int32_t width, int32_t height, int32_t spp_per_pass,
+                                   wpt_renderer **out)
+{
+    if (!s || !out) return fail(WPT_E_INVALID, "wpt_renderer_create: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_renderer_create: scene not committed");
+    if (width <= 0 || height <= 0) return fail(WPT_E_INVALID, "wpt_renderer_create: bad resolution");
+    if ((uint64_t)width * height > (1u << 24)) return fail(WPT_E_LIMIT, "wpt_renderer_create: W*H > 2^24");
+    if (spp_per_pass <= 0) spp_per_pass = 1;
+    if (spp_per_pass > 256) return fail(WPT_E_LIMIT, "wpt_renderer_create: spp_per_pass > 256");
+    const uint64_t cap = (uint64_t)width * height * spp_per_pass;
+    if (cap > 0x7fffffffull) return fail(WPT_E_LIMIT, "wpt_renderer_create: too many paths in flight");
+    wpt_renderer *r = new (std::nothrow) wpt_renderer();
+    if (!r) return fail(WPT_E_INVALID, "out of host memory");
+    r->scene = s; r->W = width; r->H = height; r->spp_per_pass = spp_per_pass; r->capacity = (uint32_t)cap;
+    cudaError_t e = cudaSetDevice(s->device);
+    for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+        e = cudaMalloc(&r->q[k].a, cap * sizeof(float4));
+        if (e == cudaSuccess) e = cudaMalloc(&r->q[k].b, cap * sizeof(float4));
+        if (e == cudaSuccess) e = cudaMalloc(&r->q[k].c, cap * sizeof(float2));
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&r->hits, cap * sizeof(int4));
+    if (e == cudaSuccess) e = cudaMalloc(&r->counters, sizeof(PassCounters));
+    if (e == cudaSuccess) e = cudaMalloc(&r->live_acc, sizeof(unsigned long long) * WPT_MAX_DEPTH);
+    if (e == cudaSuccess) e = cudaMalloc(&r->film, sizeof(float) * 3 * (size_t)width * height);
+    if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
+    if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
+    if (e != cudaSuccess) {
+        const std::string msg = std::string("wpt_renderer_create: ") + cudaGetErrorString(e);
+        wpt_renderer_destroy(r);
+        return fail(WPT_E_CUDA, msg);
+    }
+    *out = r;
+    return WPT_OK;
+}
+
+extern "C" int wpt_renderer_set_profile(wpt_renderer *r, int profile)
+{
+    if (!r) return fail(WPT_E_INVALID, "null renderer");
+    r->profile = profile != 0;
+    return WPT_OK;
+}
+
+extern "C" int wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int sort_rays)
+{
+    if (!r) return fail(WPT_E_INVALID, "null renderer");
+    (void)sort_rays;
+    r->tune.variant = trace_variant;
+    r->tune.ctas_per_sm = ctas_per_sm;
+    return WPT_OK;
+}
+
+static int check_cfg(const wpt_renderer *r, const wpt_render_config *cfg)
+{
+    if (cfg->width != r->W || cfg->height != r->H) return fail(WPT_E_INVALID, "render config resolution != renderer resolution");
+    if (cfg->depth < 1 || cfg->depth > WPT_MAX_DEPTH) return fail(WPT_E_LIMIT, "depth must be in [1, 64]");
+    if (cfg->spp_count < 0 || cfg->spp_begin < 0) return fail(WPT_E_INVALID, "negative spp range");
+    return WPT_OK;
+}
+
+extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg, float *film_r,
+                          float *film_g, float *film_b, void *stream)
+{
+    if (!r || !cam || !cfg || !film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_render: null argument");
+    if (int rc = check_cfg(r, cfg)) return rc;
+    if (r->in_flight) return fail(WPT_E_STATE, "wpt_render: previous render not finished (call wpt_render_finish)");
+    const wpt_scene *s = r->scene;
+    cudaStream_t st = (cudaStream_t)stream;
+    WPT_CUDA(cudaSetDevice(s->device));
+    WPT_CUDA(cudaMemsetAsync(r->live_acc, 0, sizeof(unsigned long long) * WPT_MAX_DEPTH, st));
+    r->passes = 0; r->launches = 0; r->depth_in_flight = cfg->depth;
+    size_t pe = 0;
+    r->prof_kind.clear();
+    auto mark = [&](int kind) -> cudaError_t {
+        if (!r->profile) return cudaSuccess;
+        for (int k = 0; k < 2; k++) {
+            if (pe + k >= r->prof_events.size()) {
+                cudaEvent_t e;
+                cudaError_t ce = cudaEventCreate(&e);
+                if (ce != cudaSuccess) return ce;
+                r->prof_events.push_back(e);
+            }
+        }
+        r->prof_kind.push_back(kind);
+        return cudaEventRecord(r->prof_events[pe], st);
+    };
+    auto done = [&]() -> cudaError_t {
+        if (!r->profile) return cudaSuccess;
+        cudaError_t ce = cudaEventRecord(r->prof_events[pe + 1], st);
+        pe += 2;
+        return ce;
+    };
+    WPT_CUDA(cudaEventRecord(r->ev_begin, st));
+    const uint32_t N = (uint32_t)r->W * r->H;
+    for (int s0 = 0; s0 < cfg->spp_count; s0 += r->spp_per_pass) {
+        const int ns = std::min(r->spp_per_pass, cfg->spp_count - s0);
+        const int spp_first = cfg->spp_begin + s0;
+        const uint32_t n_max = N * (uint32_t)ns;
+        WPT_CUDA(cudaMemsetAsync(r->counters, 0, sizeof(PassCounters), st));
+        WPT_CUDA(mark(0));
+        launch_raygen(*cam, r->W, r->H, spp_first, ns, cfg->seed, r->q[0], &r->counters->qcount[0], st);
+        WPT_CUDA(done());
+        r->launches++;
+        for (int j = 0; j < cfg->depth; j++) {
+            const RayQueue &qin = r->q[j & 1], &qout = r->q[(j + 1) & 1];
+            WPT_CUDA(mark(1));
+            launch_trace_queue(s->view, qin, r->hits, &r->counters->qcount[j], &r->counters->cursor[j],
+                               r->live_acc + j, cfg->tmin, cfg->tmax, n_max, s->num_sms, r->tune, st);
+            WPT_CUDA(done());
+            WPT_CUDA(mark(2));
+            launch_shade(qin, r->hits, &r->counters->qcount[j], qout, &r->counters->qcount[j + 1],
+                         reinterpret_cast<const float4 *>(s->d_attr), s->d_albedo, j, cfg->depth, spp_first,
+                         cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, st);
+            WPT_CUDA(done());
+            r->launches += 2;
+        }
+        r->passes++;
+    }
+    WPT_CUDA(cudaEventRecord(r->ev_end, st));
+    WPT_CUDA(cudaGetLastError());
+    r->in_flight = true;
+    return WPT_OK;
+}
+
+extern "C" int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream)
+{
+    if (!r) return fail(WPT_E_INVALID, "wpt_render_finish: null renderer");
+    if (!r->in_flight) return fail(WPT_E_STATE, "wpt_render_finish: nothing in flight");
+    cudaStream_t st = (cudaStream_t)stream;
+    WPT_CUDA(cudaSetDevice(r->scene->device));
+    WPT_CUDA(cudaStreamSynchronize(st));
+    r->in_flight = false;
+    if (!stats) return WPT_OK;
+    std::memset(stats, 0, sizeof *stats);
+    unsigned long long live[WPT_MAX_DEPTH];
+    WPT_CUDA(cudaMemcpy(live, r->live_acc, sizeof live, cudaMemcpyDeviceToHost));
+    for (int j = 0; j < r->depth_in_flight; j++) { stats->live[j] = live[j]; stats->segments += live[j]; }
+    stats->passes = r->passes;
+    stats->kernel_launches = r->launches;
+    WPT_CUDA(cudaEventElapsedTime(&stats->ms_total, r->ev_begin, r->ev_end));
+    if (r->profile) {
+        for (size_t k = 0; k < r->prof_kind.size(); k++) {
+            float ms = 0;
+            WPT_CUDA(cudaEventElapsedTime(&ms, r->prof_events[2 * k], r->prof_events[2 * k + 1]));
+            (r->prof_kind[k] == 0 ? stats->ms_raygen : r->prof_kind[k] == 1 ? stats->ms_trace : stats->ms_shade) += ms;
+        }
+    }
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_scale(float *film_r, float *film_g, float *film_b, uint32_t n, float scale, void *stream)
+{
+    if (!film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_film_scale: null film");
+    launch_film_scale(film_r, film_g, film_b, n, scale, (cudaStream_t)stream);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+extern "C" int wpt_render_host(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
+                               float *film_r, float *film_g, float *film_b, wpt_stats *stats)
+{
+    if (!r || !cam || !cfg || !film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_render_host: null argument");
+    if (int rc = check_cfg(r, cfg)) return rc;
+    const size_t N = (size_t)r->W * r->H;
+    WPT_CUDA(cudaSetDevice(r->scene->device));
+    float *dr = r->film, *dg = r->film + N, *db = r->film + 2 * N;
+    WPT_CUDA(cudaMemsetAsync(r->film, 0, sizeof(float) * 3 * N, nullptr));     // src/main.cpp:369
+    if (int rc = wpt_render(r, cam, cfg, dr, dg, db, nullptr)) return rc;
+    if (cfg->spp_count > 0)
+        if (int rc = wpt_film_scale(dr, dg, db, (uint32_t)N, 1.0f / (float)cfg->spp_count, nullptr)) return rc;
+    if (int rc = wpt_render_finish(r, stats, nullptr)) return rc;
+    WPT_CUDA(cudaMemcpy(film_r, dr, sizeof(float) * N, cudaMemcpyDeviceToHost));   // src/main.cpp:437-439
+    WPT_CUDA(cudaMemcpy(film_g, dg, sizeof(float) * N, cudaMemcpyDeviceToHost));
+    WPT_CUDA(cudaMemcpy(film_b, db, sizeof(float) * N, cudaMemcpyDeviceToHost));
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+extern "C" int wpt_raygen(const wpt_camera *cam, int32_t width, int32_t height, int32_t spp_index, uint64_t seed,
+                          float *ox, float *oy, float *oz, float *dx, float *dy, float *dz, void *stream)
+{
+    if (!cam || !ox || !oy || !oz || !dx || !dy || !dz) return fail(WPT_E_INVALID, "wpt_raygen: null argument");
+    if (width <= 0 || height <= 0 || (uint64_t)width * height > (1u << 24)) return fail(WPT_E_LIMIT, "wpt_raygen: bad resolution");
+    launch_raygen_streams(*cam, width, height, spp_index, seed, ox, oy, oz, dx, dy, dz, (cudaStream_t)stream);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+extern "C" int wpt_shade_step(const wpt_scene *s, uint32_t n, const float *o_xyz[3], const float *d_xyz[3],
+                              const int32_t *tri_id, const float *t, const float *u, const float *v,
+                              const float *s0, const float *s1, float *next_o[3], float *next_d[3],
+                              float *weight[3], void *stream)
+{
+    if (!s || !o_xyz || !d_xyz || !tri_id || !t || !u || !v || !s0 || !s1 || !next_o || !next_d || !weight)
+        return fail(WPT_E_INVALID, "wpt_shade_step: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_shade_step: scene not committed");
+    WPT_CUDA(cudaSetDevice(s->device));
+    launch_shade_streams(n, o_xyz, d_xyz, tri_id, t, u, v, s0, s1, reinterpret_cast<const float4 *>(s->d_attr),
+                         s->d_albedo, next_o, next_d, weight, (cudaStream_t)stream);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+extern "C" int wpt_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, void *stream)
+{
+    if (!out) return fail(WPT_E_INVALID, "wpt_philox: null output");
+    launch_philox(n, c1, c2, key, out, (cudaStream_t)stream);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+// src/fimage.h:33-58
+extern "C" int wpt_save_pfm(const char *path, const float *r, const float *g, const float *b, uint32_t width,
+                            uint32_t height)
+{
+    if (!path || !r || !g || !b) return fail(WPT_E_INVALID, "wpt_save_pfm: null argument");
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(WPT_E_IO, std::string("wpt_save_pfm: cannot open ") + path);
+    std::fprintf(f, "PF\n%u %u\n-1\n", width, height);
+    std::vector<float> row(3 * (size_t)width);
+    for (uint32_t y = 0; y < height; y++) {
+        const size_t src = (size_t)(height - y - 1) * width;    // bottom-up (fimage.h:49)
+        for (uint32_t x = 0; x < width; x++) {
+            row[3 * x] = r[src + x]; row[3 * x + 1] = g[src + x]; row[3 * x + 2] = b[src + x];
+        }
+        if (std::fwrite(row.data(), sizeof(float), row.size(), f) != row.size()) {
+            std::fclose(f);
+            return fail(WPT_E_IO, "wpt_save_pfm: short write");
+        }
+    }
+    std::fclose(f);
+    return WPT_OK;
+}

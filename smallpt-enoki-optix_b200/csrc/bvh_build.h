@@ -1,0 +1,28 @@
+// bvh_build.h — host-side SAH BVH builder and wide-node flattener (C++, no CUDA).
+// New work: the reference has no builder of its own (OptiX builds the GAS inside the driver,
+// src/accel/optix_backend.h:309-358).
+#pragma once
+#include <vector>
+#include "bvh.h"
+
+namespace wpt {
+
+struct BuiltBvh {
+    std::vector<Node8>   nodes;    // nodes[0] is the root
+    std::vector<Tri48>   tris;     // leaf order
+    std::vector<int32_t> prim_id;  // leaf slot -> original face index
+    uint32_t max_depth = 0;        // wide-tree depth (root = 1)
+    double   sah_cost = 0.0;
+    double   build_ms = 0.0;
+};
+
+// positions f32[3*n_pos], triplets i32[3*n_tris].  Returns false + message on invalid input
+// (index out of range, non-finite vertex, depth limit).
+bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
+                BuiltBvh &out, const char **err, int threads = 0);
+
+// Decode helpers shared with the tests: child box of slot i in world space (conservative bounds the
+// traversal kernel effectively tests).
+void node_child_bounds(const Node8 &n, int slot, float lo[3], float hi[3]);
+
+}  // namespace wpt

@@ -1,0 +1,100 @@
+// hosttest.cpp — TEST-ONLY library (libwpt_hosttest.so): runs the host builder and the
+// __host__ __device__ traversal core on the CPU so the logic can be checked without a GPU.
+// It is NOT linked into libwpt.so and no product entry point reaches it.
+#include <cmath>
+#include <cstdio>
+#include <vector>
+#include "bvh_build.h"
+#include "trace_core.h"
+
+using namespace wpt;
+
+extern "C" {
+
+// returns 0 ok; fills stats[0..5] = n_nodes, n_tris, max_depth, sah_cost, build_ms, n_problems
+int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris, double *stats)
+{
+    BuiltBvh b;
+    const char *err = nullptr;
+    if (!build_bvh8(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
+    // structural validation: every triangle appears exactly once; every child's quantised box
+    // contains the geometry below it; internal children are contiguous.
+    std::vector<int> seen(n_tris, 0);
+    long problems = 0;
+    struct Item { uint32_t node; };
+    std::vector<uint32_t> stack{0u};
+    std::vector<float> lo_of(b.nodes.size() * 3), hi_of(b.nodes.size() * 3);
+    // bottom-up true bounds via recursion (explicit post-order)
+    std::vector<std::pair<uint32_t, int>> st{{0u, 0}};
+    std::vector<uint32_t> order;
+    while (!st.empty()) {
+        auto [n, _] = st.back(); st.pop_back();
+        order.push_back(n);
+        const Node8 &nd = b.nodes[n];
+        int rel = 0;
+        for (int s = 0; s < 8; s++) if (nd.imask & (1 << s)) st.push_back({nd.child_base + rel++, 0});
+    }
+    for (size_t oi = order.size(); oi-- > 0;) {
+        const uint32_t n = order[oi];
+        const Node8 &nd = b.nodes[n];
+        float nlo[3] = {INFINITY, INFINITY, INFINITY}, nhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        int rel = 0;
+        for (int s = 0; s < 8; s++) {
+            if (!nd.meta[s]) continue;
+            float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            if (nd.imask & (1 << s)) {
+                const uint32_t c = nd.child_base + rel++;
+                for (int k = 0; k < 3; k++) { clo[k] = lo_of[3 * c + k]; chi[k] = hi_of[3 * c + k]; }
+            } else {
+                const int cnt = pop_count(nd.meta[s] >> 5), off = nd.meta[s] & 31;
+                for (int i = 0; i < cnt; i++) {
+                    const uint32_t slot = nd.tri_base + off + i;
+                    const int32_t prim = b.prim_id[slot];
+                    if (prim < 0 || (uint32_t)prim >= n_tris) { problems++; continue; }
+                    seen[prim]++;
+                    for (int v = 0; v < 3; v++) {
+                        const float *p = pos + 3 * (size_t)idx[3 * prim + v];
+                        for (int k = 0; k < 3; k++) { clo[k] = fminf(clo[k], p[k]); chi[k] = fmaxf(chi[k], p[k]); }
+                    }
+                }
+            }
+            float qlo[3], qhi[3];
+            node_child_bounds(nd, s, qlo, qhi);
+            for (int k = 0; k < 3; k++) {
+                if (!(qlo[k] <= clo[k] && qhi[k] >= chi[k])) problems++;
+                nlo[k] = fminf(nlo[k], clo[k]); nhi[k] = fmaxf(nhi[k], chi[k]);
+            }
+        }
+        for (int k = 0; k < 3; k++) { lo_of[3 * n + k] = nlo[k]; hi_of[3 * n + k] = nhi[k]; }
+    }
+    for (uint32_t i = 0; i < n_tris; i++) if (seen[i] != 1) problems++;
+    stats[0] = (double)b.nodes.size(); stats[1] = (double)b.tris.size(); stats[2] = b.max_depth;
+    stats[3] = b.sah_cost; stats[4] = b.build_ms; stats[5] = (double)problems;
+    return 0;
+}
+
+int wpt_hosttest_trace(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
+                       const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
+                       const float *dz, float tmin, float tmax, uint32_t n,
+                       int32_t *id, float *t, float *u, float *v)
+{
+    BuiltBvh b;
+    const char *err = nullptr;
+    if (!build_bvh8(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
+    BvhView view;
+    view.nodes = reinterpret_cast<const uint4 *>(b.nodes.data());
+    view.tris = reinterpret_cast<const float4 *>(b.tris.data());
+    view.prim_id = b.prim_id.data();
+    view.n_nodes = (uint32_t)b.nodes.size();
+    view.n_tris = (uint32_t)b.tris.size();
+#pragma omp parallel for schedule(dynamic, 1024)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        const RayCtx r = make_ray(ox[i], oy[i], oz[i], dx[i], dy[i], dz[i], tmin);
+        LocalStack st;
+        const Hit h = trace_ray(view, r, tmax, st);
+        id[i] = h.slot < 0 ? -1 : view.prim_id[h.slot];
+        if (h.slot >= 0) { t[i] = h.t; u[i] = h.u; v[i] = h.v; }
+    }
+    return 0;
+}
+}

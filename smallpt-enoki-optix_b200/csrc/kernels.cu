@@ -1,0 +1,450 @@
+// kernels.cu — hand-written sm_100a kernels of the wavefront path tracer:
+//   trace_persistent  closest-hit BVH traversal (replaces optixLaunch, src/accel/optix_backend.h:460,
+//                     and the OptiX programs src/wavefront_isect.cu:48-112)
+//   raygen_kernel     camera rays (src/main.cpp:395-396 -> src/pinhole.h:27-56)
+//   shade_kernel      fused miss-accumulate / attribute interpolation / frame / Lambert sample /
+//                     next-ray write with block-aggregated warp-ballot compaction
+//                     (src/main.cpp:407-424, src/accel/optix_backend.h:463-486)
+// Nothing here is a dense contraction: no tensor cores.  The traversal is an L2-latency / issue
+// bound pointer chase; the stream kernels are HBM bound.
+#include "kernels.cuh"
+#include "shade_core.h"
+#include "trace_core.h"
+
+namespace wpt {
+
+// ------------------------------------------------------------------------------------------------
+// ray sources / hit sinks
+// ------------------------------------------------------------------------------------------------
+struct QueueIO {
+    RayQueue q;
+    int4 *hits;
+    float tmin, tmax;
+    __device__ __forceinline__ bool load(uint32_t i, float &ox, float &oy, float &oz, float &dx, float &dy,
+                                         float &dz, float &t0, float &t1) const
+    {
+        const float4 a = __ldcs(q.a + i);   // streaming: do not displace the BVH in L2
+        const float4 b = __ldcs(q.b + i);
+        ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z; t0 = tmin; t1 = tmax;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, int32_t prim, float t, float u, float v) const
+    {
+        __stcs(hits + i, make_int4(prim, __float_as_int(t), __float_as_int(u), __float_as_int(v)));
+    }
+};
+
+struct StreamIODev {
+    StreamIO s;
+    __device__ __forceinline__ bool load(uint32_t i, float &ox, float &oy, float &oz, float &dx, float &dy,
+                                         float &dz, float &t0, float &t1) const
+    {
+        // wavefront_isect.cu:86-87: size-1 mask broadcasts; masked-out lanes are skipped entirely
+        if (s.mask) {
+            const uint8_t m = s.mask_size == 1 ? s.mask[0] : s.mask[i];
+            if (!m) return false;
+        }
+        ox = __ldcs(s.ox + i); oy = __ldcs(s.oy + i); oz = __ldcs(s.oz + i);
+        dx = __ldcs(s.dx + i); dy = __ldcs(s.dy + i); dz = __ldcs(s.dz + i);
+        t0 = s.tmin ? __ldcs(s.tmin + i) : s.tmin_s;
+        t1 = s.tmax ? __ldcs(s.tmax + i) : s.tmax_s;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, int32_t prim, float t, float u, float v) const
+    {
+        s.tri_id[i] = prim;                 // -1 on miss (wavefront_isect.cu:70)
+        if (prim >= 0) { s.t[i] = t; s.u[i] = u; s.v[i] = v; }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// persistent-thread traversal with dynamic ray fetch
+// ------------------------------------------------------------------------------------------------
+constexpr int kTraceBlock = 128;
+constexpr int kSmemStack = 10;     // entries kept in shared memory per thread; the rest spills to local
+
+template <class IO, int FETCH_THRESHOLD>
+__global__ void __launch_bounds__(kTraceBlock, 5)
+trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
+                 uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
+{
+    __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+    const uint32_t n = n_ptr ? *n_ptr : n_static;
+    if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
+    const unsigned lane = threadIdx.x & 31u;
+    uint2 *const my = sstack + threadIdx.x;
+    uint2 lstack[kStackSize - kSmemStack];
+    int sp = 0;
+
+    bool active = false, exhausted = false;
+    uint32_t ray_i = 0, oct_inv = 0;
+    RayCtx r;
+    Hit hit;
+    uint2 G;
+    G.x = G.y = 0u;
+    hit.slot = -1; hit.t = hit.u = hit.v = 0.0f;
+
+    for (;;) {
+        // ---- refill idle lanes: one warp-aggregated atomic on the global cursor
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && !exhausted) {
+            const int cnt = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)cnt);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (base + (uint32_t)cnt >= n) exhausted = true;
+            if (!active) {
+                const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                float ox, oy, oz, dx, dy, dz, t0, t1;
+                if (i < n && io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) {
+                    r = make_ray(ox, oy, oz, dx, dy, dz, t0);
+                    oct_inv = r.oct_inv4 & 7u;
+                    hit.slot = -1; hit.t = t1; hit.u = hit.v = 0.0f;
+                    G.x = 0u; G.y = 0x80000000u;
+                    sp = 0;
+                    ray_i = i;
+                    active = true;
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (exhausted) break;
+            continue;
+        }
+
+        // ---- traverse until done, or until too few lanes of the warp are still working
+        while (active) {
+            uint2 T;
+            T.x = T.y = 0u;
+            if (G.y & 0xff000000u) {
+                const int bit = 31 - __clz((int)G.y);
+                G.y &= ~(1u << bit);
+                if (G.y & 0xff000000u) {
+                    if (sp < kSmemStack) my[sp * kTraceBlock] = G; else lstack[sp - kSmemStack] = G;
+                    sp++;
+                }
+                const uint32_t slot = ((uint32_t)bit - 24u) ^ oct_inv;
+                const uint32_t rel = (uint32_t)__popc(G.y & ~(0xffffffffu << slot) & 0xffu);
+                const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 5;
+                const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
+                            n4 = __ldg(np + 4);
+                const uint32_t hm = node_hits(n0, n1, n2, n3, n4, r, hit.t);
+                G.x = n1.x; G.y = (hm & 0xff000000u) | (n0.w >> 24);
+                T.x = n1.y; T.y = hm & 0x00ffffffu;
+            } else {
+                T = G; G.x = G.y = 0u;
+            }
+            while (T.y) {
+                const int bit = 31 - __clz((int)T.y);
+                T.y &= ~(1u << bit);
+                const uint32_t ti = T.x + (uint32_t)bit;
+                const float4 *tp = bvh.tris + (size_t)ti * 3;
+                const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+                if (tri_hit(t0, t1, t2, r, hit.t, hit.u, hit.v)) hit.slot = (int32_t)ti;
+            }
+            if (!(G.y & 0xff000000u)) {
+                if (sp == 0) {
+                    const int32_t prim = hit.slot < 0 ? -1 : __ldg(bvh.prim_id + hit.slot);
+                    io.store(ray_i, prim, hit.t, hit.u, hit.v);
+                    active = false;
+                    break;
+                }
+                sp--;
+                G = sp < kSmemStack ? my[sp * kTraceBlock] : lstack[sp - kSmemStack];
+            }
+            if (FETCH_THRESHOLD > 0 && __popc(__activemask()) < FETCH_THRESHOLD) break;
+        }
+        __syncwarp();
+    }
+}
+
+// one thread per ray, whole traversal in one go (comparison variant / small launches)
+template <class IO>
+__global__ void __launch_bounds__(kTraceBlock)
+trace_simple(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
+             unsigned long long *__restrict__ live_acc)
+{
+    const uint32_t n = n_ptr ? *n_ptr : n_static;
+    if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float ox, oy, oz, dx, dy, dz, t0, t1;
+        if (!io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) continue;
+        const RayCtx r = make_ray(ox, oy, oz, dx, dy, dz, t0);
+        LocalStack st;
+        const Hit h = trace_ray(bvh, r, t1, st);
+        const int32_t prim = h.slot < 0 ? -1 : __ldg(bvh.prim_id + h.slot);
+        io.store(i, prim, h.t, h.u, h.v);
+    }
+}
+
+template <class IO>
+static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n_ptr, uint32_t n_static,
+                             uint32_t *cursor, unsigned long long *live_acc, int num_sms,
+                             const TraceTuning &tune, cudaStream_t st)
+{
+    if (tune.variant == 1) {
+        const uint32_t blocks = (uint32_t)num_sms * 16u;
+        trace_simple<IO><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, live_acc);
+        return;
+    }
+    int per_sm = tune.ctas_per_sm;
+    if (per_sm <= 0) {
+        static int cached = 0;
+        if (!cached) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cached, trace_persistent<IO, 20>, kTraceBlock, 0);
+            if (cached <= 0) cached = 4;
+        }
+        per_sm = cached;
+    }
+    const uint32_t blocks = (uint32_t)(num_sms * per_sm);
+    if (tune.variant == 2)
+        trace_persistent<IO, 0><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+    else
+        trace_persistent<IO, 20><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+}
+
+void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,
+                        uint32_t *cursor, unsigned long long *live_acc, float tmin, float tmax,
+                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st)
+{
+    QueueIO io;
+    io.q = q; io.hits = hits; io.tmin = tmin; io.tmax = tmax;
+    launch_trace_any(bvh, io, n_ptr, n_max, cursor, live_acc, num_sms, tune, st);
+}
+
+void launch_trace_streams(const BvhView &bvh, const StreamIO &s, uint32_t n, uint32_t *cursor, int num_sms,
+                          const TraceTuning &tune, cudaStream_t st)
+{
+    StreamIODev io;
+    io.s = s;
+    launch_trace_any(bvh, io, nullptr, n, cursor, nullptr, num_sms, tune, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+// camera rays
+// ------------------------------------------------------------------------------------------------
+// Lane order inside a frame: 8x4 pixel tiles per warp when the resolution allows it (more coherent
+// primary rays than scanline rows); the pixel index travels in the path id, so order is free.
+__device__ __forceinline__ void lane_to_pixel(uint32_t p, int W, int H, int &x, int &y)
+{
+    if (((W & 7) | (H & 3)) == 0) {
+        const uint32_t tile = p >> 5, in = p & 31u, tw = (uint32_t)W >> 3;
+        x = (int)((tile % tw) * 8u + (in & 7u));
+        y = (int)((tile / tw) * 4u + (in >> 3));
+    } else {
+        x = (int)(p % (uint32_t)W);
+        y = (int)(p / (uint32_t)W);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass, uint32_t k0, uint32_t k1,
+              RayQueue q, uint32_t *__restrict__ qcount0)
+{
+    const uint32_t N = (uint32_t)W * (uint32_t)H;
+    const uint32_t total = N * (uint32_t)spp_in_pass;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *qcount0 = total;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t s_local = i / N, p = i - s_local * N;
+        int x, y;
+        lane_to_pixel(p, W, H, x, y);
+        const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;   // src/main.cpp:379-381
+        uint32_t rnd[4];
+        philox4x32_10(pixel, (uint32_t)spp_first + s_local, 0u, 0u, k0, k1, rnd);
+        const float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
+        V3 o, d;
+        camera_ray(cam, x, y, W, H, xi, o, d);
+        __stcs(q.a + i, make_float4(o.x, o.y, o.z, __uint_as_float(pixel | (s_local << 24))));
+        __stcs(q.b + i, make_float4(d.x, d.y, d.z, 1.0f));        // contrib = 1 (src/main.cpp:391)
+        __stcs(q.c + i, make_float2(1.0f, 1.0f));
+    }
+}
+
+void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
+                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st)
+{
+    const uint64_t total = (uint64_t)W * H * spp_in_pass;
+    const uint32_t blocks = (uint32_t)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    raygen_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_first, spp_in_pass, (uint32_t)seed,
+                                                       (uint32_t)(seed >> 32), q, qcount0);
+}
+
+__global__ void __launch_bounds__(256)
+raygen_streams_kernel(const wpt_camera cam, int W, int H, int spp, uint32_t k0, uint32_t k1, float *ox,
+                      float *oy, float *oz, float *dx, float *dy, float *dz)
+{
+    const uint32_t N = (uint32_t)W * (uint32_t)H;
+    for (uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < N; pixel += gridDim.x * blockDim.x) {
+        const int y = (int)(pixel / (uint32_t)W), x = (int)(pixel % (uint32_t)W);
+        uint32_t rnd[4];
+        philox4x32_10(pixel, (uint32_t)spp, 0u, 0u, k0, k1, rnd);
+        const float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
+        V3 o, d;
+        camera_ray(cam, x, y, W, H, xi, o, d);
+        ox[pixel] = o.x; oy[pixel] = o.y; oz[pixel] = o.z;
+        dx[pixel] = d.x; dy[pixel] = d.y; dz[pixel] = d.z;
+    }
+}
+
+void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, uint64_t seed, float *ox,
+                           float *oy, float *oz, float *dx, float *dy, float *dz, cudaStream_t st)
+{
+    const uint32_t N = (uint32_t)W * H;
+    const uint32_t blocks = (N + 255) / 256;
+    raygen_streams_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_index, (uint32_t)seed,
+                                                               (uint32_t)(seed >> 32), ox, oy, oz, dx, dy, dz);
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused shade + sample + accumulate + compact
+// ------------------------------------------------------------------------------------------------
+constexpr int kShadeBlock = 256;
+
+__global__ void __launch_bounds__(kShadeBlock)
+shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *__restrict__ n_ptr,
+             const RayQueue out, uint32_t *__restrict__ n_out, const float4 *__restrict__ tri_attr,
+             const float *__restrict__ albedo, int bounce, int depth, int spp_first, uint32_t k0, uint32_t k1,
+             float *__restrict__ film_r, float *__restrict__ film_g, float *__restrict__ film_b)
+{
+    __shared__ uint32_t warp_cnt[kShadeBlock / 32];
+    __shared__ uint32_t block_base;
+    const uint32_t n = *n_ptr;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const bool last = bounce + 1 >= depth;   // path is cut after `depth` segments (src/main.cpp:399)
+    const uint32_t stride = gridDim.x * blockDim.x;
+    // all threads of a block run the same number of iterations (block-uniform loop bound)
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        const uint32_t i = base + threadIdx.x;
+        bool survive = false;
+        float4 na, nb;
+        float2 nc;
+        if (i < n) {
+            const int4 h = __ldcs(hits + i);
+            const float4 a = __ldcs(in.a + i);
+            const float4 b = __ldcs(in.b + i);
+            const float2 c = __ldcs(in.c + i);
+            const uint32_t pid = __float_as_uint(a.w);
+            const uint32_t pixel = pid & 0x00ffffffu;
+            if (h.x < 0) {
+                // escaped: film += contrib (src/main.cpp:407); fire-and-forget RED.ADD.F32
+                atomicAdd(film_r + pixel, b.w);
+                atomicAdd(film_g + pixel, c.x);
+                atomicAdd(film_b + pixel, c.y);
+            } else if (!last) {
+                const float4 *ap = tri_attr + (size_t)h.x * 3;
+                const float4 q0 = __ldg(ap), q1 = __ldg(ap + 1), q2 = __ldg(ap + 2);
+                const int mat = __float_as_int(q2.y);
+                uint32_t rnd[4];
+                philox4x32_10(pixel, (uint32_t)spp_first + (pid >> 24), 1u + (uint32_t)bounce, 0u, k0, k1, rnd);
+                V3 no, nd;
+                shade_step(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), __int_as_float(h.y), __int_as_float(h.z),
+                           __int_as_float(h.w), v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), v3(q1.z, q1.w, q2.x),
+                           u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), no, nd);
+                const float wr = __ldg(albedo + 3 * mat), wg = __ldg(albedo + 3 * mat + 1),
+                            wb = __ldg(albedo + 3 * mat + 2);
+                na = make_float4(no.x, no.y, no.z, a.w);
+                nb = make_float4(nd.x, nd.y, nd.z, b.w * wr);     // contrib *= bsdf weight (src/main.cpp:422)
+                nc = make_float2(c.x * wg, c.y * wb);
+                survive = true;
+            }
+        }
+        if (last) continue;   // block-uniform
+        // ---- compaction: warp ballot -> per-block offsets -> one atomic per block on the queue tail
+        const unsigned bal = __ballot_sync(0xffffffffu, survive);
+        if (lane == 0) warp_cnt[warp] = (uint32_t)__popc(bal);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t tot = 0;
+#pragma unroll
+            for (int w = 0; w < kShadeBlock / 32; w++) { const uint32_t c = warp_cnt[w]; warp_cnt[w] = tot; tot += c; }
+            block_base = tot ? atomicAdd(n_out, tot) : 0u;
+        }
+        __syncthreads();
+        if (survive) {
+            const uint32_t o = block_base + warp_cnt[warp] + (uint32_t)__popc(bal & ((1u << lane) - 1u));
+            __stcs(out.a + o, na);
+            __stcs(out.b + o, nb);
+            __stcs(out.c + o, nc);
+        }
+        __syncthreads();   // warp_cnt / block_base are reused by the next iteration
+    }
+}
+
+void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
+                  uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
+                  int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
+                  int num_sms, cudaStream_t st)
+{
+    uint32_t blocks = (n_max + kShadeBlock - 1) / kShadeBlock;
+    const uint32_t cap = (uint32_t)num_sms * 8u;
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    shade_kernel<<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
+                                                 spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
+                                                 film_g, film_b);
+}
+
+// per-function entry point: one shading step on SoA streams (parity tests)
+struct ShadeStreams {
+    const float *o[3], *d[3];
+    const int32_t *tri_id;
+    const float *t, *u, *v, *s0, *s1;
+    float *no[3], *nd[3], *w[3];
+};
+__global__ void shade_streams_kernel(uint32_t n, ShadeStreams p, const float4 *__restrict__ tri_attr,
+                                     const float *__restrict__ albedo)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t tri = p.tri_id[i];
+    if (tri < 0) return;
+    const float4 *ap = tri_attr + (size_t)tri * 3;
+    const float4 q0 = __ldg(ap), q1 = __ldg(ap + 1), q2 = __ldg(ap + 2);
+    const int mat = __float_as_int(q2.y);
+    V3 no, nd;
+    shade_step(v3(p.o[0][i], p.o[1][i], p.o[2][i]), v3(p.d[0][i], p.d[1][i], p.d[2][i]), p.t[i], p.u[i], p.v[i],
+               v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), v3(q1.z, q1.w, q2.x), p.s0[i], p.s1[i], no, nd);
+    p.no[0][i] = no.x; p.no[1][i] = no.y; p.no[2][i] = no.z;
+    p.nd[0][i] = nd.x; p.nd[1][i] = nd.y; p.nd[2][i] = nd.z;
+    p.w[0][i] = albedo[3 * mat]; p.w[1][i] = albedo[3 * mat + 1]; p.w[2][i] = albedo[3 * mat + 2];
+}
+void launch_shade_streams(uint32_t n, const float *const o[3], const float *const d[3], const int32_t *tri_id,
+                          const float *t, const float *u, const float *v, const float *s0, const float *s1,
+                          const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
+                          float *const w[3], cudaStream_t st)
+{
+    ShadeStreams p;
+    for (int k = 0; k < 3; k++) { p.o[k] = o[k]; p.d[k] = d[k]; p.no[k] = no[k]; p.nd[k] = nd[k]; p.w[k] = w[k]; }
+    p.tri_id = tri_id; p.t = t; p.u = u; p.v = v; p.s0 = s0; p.s1 = s1;
+    if (n) shade_streams_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, p, tri_attr, albedo);
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void film_scale_kernel(float *r, float *g, float *b, uint32_t n, float scale)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        r[i] *= scale; g[i] *= scale; b[i] *= scale;     // film /= num_samples (src/main.cpp:429)
+    }
+}
+void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st)
+{
+    uint32_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (n) film_scale_kernel<<<blocks, 256, 0, st>>>(r, g, b, n, scale);
+}
+
+__global__ void philox_kernel(uint32_t n, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1, uint32_t *out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t r[4];
+    philox4x32_10(i, c1, c2, 0u, k0, k1, r);
+    out[4 * i] = r[0]; out[4 * i + 1] = r[1]; out[4 * i + 2] = r[2]; out[4 * i + 3] = r[3];
+}
+void launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, cudaStream_t st)
+{
+    if (n) philox_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, c1, c2, (uint32_t)key, (uint32_t)(key >> 32), out);
+}
+
+}  // namespace wpt

@@ -1,0 +1,62 @@
+// kernels.cuh — launch-side declarations shared by kernels.cu and api.cu
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "bvh.h"
+#include "../../include/wpt.h"
+
+namespace wpt {
+
+// In-flight path record, 40 B in three coalesced streams (16 B + 16 B + 8 B per lane):
+//   a = (o.x, o.y, o.z, path id bits)   path id = pixel | (sample-in-pass << 24)
+//   b = (d.x, d.y, d.z, throughput.r)
+//   c = (throughput.g, throughput.b)
+struct RayQueue {
+    float4 *a;
+    float4 *b;
+    float2 *c;
+};
+
+// Per-pass device counters.  qcount[j] = rays entering bounce j; cursor[j] = dynamic-fetch cursor of
+// the trace kernel of bounce j.
+struct PassCounters {
+    uint32_t qcount[WPT_MAX_DEPTH + 1];
+    uint32_t cursor[WPT_MAX_DEPTH + 1];
+};
+
+struct TraceTuning {
+    int variant;      // 0 = persistent + dynamic fetch (default), 1 = one thread per ray
+    int ctas_per_sm;  // persistent grid = num_sms * ctas_per_sm
+};
+
+// SoA stream front-end of wpt_intersect (mirror of struct Params, src/optixdata.h:11-29)
+struct StreamIO {
+    const float *ox, *oy, *oz, *dx, *dy, *dz, *tmin, *tmax;
+    float tmin_s, tmax_s;
+    const uint8_t *mask;
+    uint32_t mask_size;
+    int32_t *tri_id;
+    float *t, *u, *v;
+};
+
+void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,
+                        uint32_t *cursor, unsigned long long *live_acc, float tmin, float tmax,
+                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st);
+void launch_trace_streams(const BvhView &bvh, const StreamIO &io, uint32_t n, uint32_t *cursor, int num_sms,
+                          const TraceTuning &tune, cudaStream_t st);
+void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
+                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st);
+void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, uint64_t seed, float *ox,
+                           float *oy, float *oz, float *dx, float *dy, float *dz, cudaStream_t st);
+void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
+                  uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
+                  int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
+                  int num_sms, cudaStream_t st);
+void launch_shade_streams(uint32_t n, const float *const o[3], const float *const d[3], const int32_t *tri_id,
+                          const float *t, const float *u, const float *v, const float *s0, const float *s1,
+                          const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
+                          float *const w[3], cudaStream_t st);
+void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st);
+void launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, cudaStream_t st);
+
+}  // namespace wpt

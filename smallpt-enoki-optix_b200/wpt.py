@@ -1,0 +1,358 @@
+"""Python host-side mirror of the reference's interface for the hot path, over the C ABI of
+libwpt.so (include/wpt.h) via ctypes.  Class and method names follow the reference
+(src/main.cpp: Scene.add_triangle_mesh / commit / intersect; src/pinhole.h: ThinlensCamera;
+src/fimage.h: Fimage.save_pfm) so tests read like the reference's own driver.
+
+PyTorch is plumbing only: device buffers, streams, torch.distributed.  All compute is in libwpt.so;
+there is no fallback — a missing library or a missing GPU raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwpt.so")
+WPT_MAX_DEPTH = 64
+
+
+class WptError(RuntimeError):
+    """Raised for any non-zero libwpt status (the reference throws std::runtime_error,
+    src/accel/optix_backend.h:25-82)."""
+
+    def __init__(self, code, msg):
+        super().__init__(f"wpt error {code}: {msg}")
+        self.code = code
+
+
+class MeshDesc(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("position_triplets", C.c_void_p), ("normals", C.c_void_p),
+                ("normal_triplets", C.c_void_p), ("material_id", C.c_void_p), ("albedo", C.c_void_p),
+                ("n_positions", C.c_uint32), ("n_triangles", C.c_uint32), ("n_normals", C.c_uint32),
+                ("n_materials", C.c_uint32)]
+
+
+class BvhStats(C.Structure):
+    _fields_ = [("n_triangles", C.c_uint32), ("n_nodes", C.c_uint32), ("n_leaf_slots", C.c_uint32),
+                ("max_depth", C.c_uint32), ("sah_cost", C.c_double), ("build_ms", C.c_double),
+                ("upload_ms", C.c_double), ("node_bytes", C.c_uint64), ("tri_bytes", C.c_uint64),
+                ("attr_bytes", C.c_uint64)]
+
+
+class RayStreams(C.Structure):
+    _fields_ = [("ox", C.c_void_p), ("oy", C.c_void_p), ("oz", C.c_void_p), ("dx", C.c_void_p),
+                ("dy", C.c_void_p), ("dz", C.c_void_p), ("tmin", C.c_void_p), ("tmax", C.c_void_p),
+                ("tmin_scalar", C.c_float), ("tmax_scalar", C.c_float)]
+
+
+class HitStreams(C.Structure):
+    _fields_ = [("tri_id", C.c_void_p), ("t", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("x", C.c_float * 3), ("y", C.c_float * 3), ("z", C.c_float * 3),
+                ("film_size_y", C.c_float), ("focal_dist", C.c_float), ("fov_y", C.c_float),
+                ("lens_radius", C.c_float)]
+
+
+class RenderConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp_begin", C.c_int32), ("spp_count", C.c_int32),
+                ("depth", C.c_int32), ("seed", C.c_uint64), ("tmin", C.c_float), ("tmax", C.c_float)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("segments", C.c_uint64), ("live", C.c_uint64 * WPT_MAX_DEPTH), ("passes", C.c_uint32),
+                ("kernel_launches", C.c_uint32), ("ms_total", C.c_float), ("ms_raygen", C.c_float),
+                ("ms_trace", C.c_float), ("ms_shade", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libwpt.so (in-tree).  Fails loudly if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise WptError(-1, f"{LIB_PATH} not built: run __graft_entry__.build() or make -C smallpt-enoki-optix_b200")
+        L = C.CDLL(LIB_PATH)
+        L.wpt_last_error.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise WptError(rc, lib().wpt_last_error().decode())
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(a) for a in v])
+
+
+def _np(a, dt):
+    return np.ascontiguousarray(a, dtype=dt)
+
+
+def _ptr(t):
+    """device (or host) pointer of a torch tensor / numpy array / None"""
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        return C.c_void_p(t.ctypes.data)
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream_handle(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+class ThinlensCamera:
+    """src/pinhole.h:7-72.  Same constructor argument order as the reference."""
+
+    def __init__(self, look_from, look_at, up, lens_radius, focal_dist, fov_y, film_size_y=0.035):
+        self.c = Camera()
+        _check(lib().wpt_camera_init(C.byref(self.c), _f3(look_from), _f3(look_at), _f3(up), C.c_float(lens_radius),
+                                     C.c_float(focal_dist), C.c_float(fov_y), C.c_float(film_size_y)))
+
+    @classmethod
+    def reference_default(cls):
+        """the camera main() builds, src/main.cpp:383"""
+        return cls((0.0, 3.03, 5.0), (0.0, 0.03, 0.0), (0.0, 1.0, 0.0), 0.0, 1.0, 40.0 / 180.0 * np.pi)
+
+
+class Scene:
+    """src/main.cpp:286-352."""
+
+    def __init__(self):
+        self._h = C.c_void_p()
+        self._keep = None
+        self.device = None
+        self.n_triangles = 0
+
+    def add_triangle_mesh(self, positions, position_triplets, normals=None, normal_triplets=None,
+                          material_id=None, albedo=None):
+        """Host arrays as produced by load_meshes (src/main.cpp:133-251); see also wpt_obj.load_meshes."""
+        if self._h:
+            raise WptError(3, "Scene already holds a mesh")
+        pos = _np(positions, np.float32).reshape(-1)
+        idx = _np(position_triplets, np.int32).reshape(-1)
+        d = MeshDesc()
+        d.positions, d.position_triplets = pos.ctypes.data, idx.ctypes.data
+        d.n_positions, d.n_triangles = pos.size // 3, idx.size // 3
+        keep = [pos, idx]
+        if normals is not None and normal_triplets is not None:
+            nrm = _np(normals, np.float32).reshape(-1)
+            nidx = _np(normal_triplets, np.int32).reshape(-1)
+            d.normals, d.normal_triplets, d.n_normals = nrm.ctypes.data, nidx.ctypes.data, nrm.size // 3
+            keep += [nrm, nidx]
+        if material_id is not None:
+            mat = _np(material_id, np.int32).reshape(-1)
+            d.material_id = mat.ctypes.data
+            keep.append(mat)
+        if albedo is not None:
+            alb = _np(albedo, np.float32).reshape(-1)
+            d.albedo, d.n_materials = alb.ctypes.data, alb.size // 3
+            keep.append(alb)
+        _check(lib().wpt_scene_create(C.byref(d), C.byref(self._h)))
+        self.n_triangles = d.n_triangles
+
+    def commit(self, device=0):
+        if not self._h:
+            raise WptError(3, "Scene.commit: no mesh")
+        _check(lib().wpt_scene_commit(self._h, C.c_int(device)))
+        self.device = device
+
+    def stats(self):
+        s = BvhStats()
+        _check(lib().wpt_scene_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in BvhStats._fields_}
+
+    def intersect(self, origin, direction, active=None, tmin=1e-3, tmax=1e20, out=None, stream=None):
+        """OptixBackend::intersect's launch (src/accel/optix_backend.h:422-460).
+        origin, direction: 3-tuples of 1-D CUDA float32 tensors (the SoA streams of Ray3C);
+        active: None, or a uint8/bool CUDA tensor of size n or 1.  Returns (tri_id, t, u, v) CUDA tensors;
+        lanes masked out keep whatever `out` held."""
+        import torch
+        n = origin[0].numel()
+        for t_ in list(origin) + list(direction):
+            assert t_.is_cuda and t_.dtype == torch.float32 and t_.is_contiguous() and t_.numel() == n
+        if out is None:
+            dev = origin[0].device
+            out = (torch.full((n,), -2, dtype=torch.int32, device=dev),
+                   torch.full((n,), float("nan"), dtype=torch.float32, device=dev),
+                   torch.full((n,), float("nan"), dtype=torch.float32, device=dev),
+                   torch.full((n,), float("nan"), dtype=torch.float32, device=dev))
+        rs = RayStreams(*[t_.data_ptr() for t_ in list(origin) + list(direction)], None, None, tmin, tmax)
+        if torch.is_tensor(tmin):
+            rs.tmin = tmin.data_ptr()
+        if torch.is_tensor(tmax):
+            rs.tmax = tmax.data_ptr()
+        hs = HitStreams(*[t_.data_ptr() for t_ in out])
+        mptr, msz = None, 0
+        if active is not None:
+            if active.dtype == torch.bool:
+                active = active.view(torch.uint8)
+            assert active.is_cuda and active.dtype == torch.uint8
+            mptr, msz = C.c_void_p(active.data_ptr()), active.numel()
+        _check(lib().wpt_intersect(self._h, C.byref(rs), mptr, C.c_uint32(msz), C.c_uint32(n), C.byref(hs),
+                                   _stream_handle(stream)))
+        return out
+
+    def intersect_host(self, o, d, active=None, tmin=1e-3, tmax=1e20):
+        """Host numpy in/out through wpt_intersect_host (copies inside).  o, d: (n,3) float32."""
+        o = _np(o, np.float32).reshape(-1, 3)
+        d = _np(d, np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        cols = [np.ascontiguousarray(o[:, k]) for k in range(3)] + [np.ascontiguousarray(d[:, k]) for k in range(3)]
+        rs = RayStreams(*[c.ctypes.data for c in cols], None, None, tmin, tmax)
+        hid = np.full(n, -2, np.int32)
+        t = np.full(n, np.nan, np.float32)
+        u = np.full(n, np.nan, np.float32)
+        v = np.full(n, np.nan, np.float32)
+        hs = HitStreams(hid.ctypes.data, t.ctypes.data, u.ctypes.data, v.ctypes.data)
+        mptr, msz = None, 0
+        if active is not None:
+            active = _np(active, np.uint8)
+            mptr, msz = C.c_void_p(active.ctypes.data), active.size
+        _check(lib().wpt_intersect_host(self._h, C.byref(rs), mptr, C.c_uint32(msz), C.c_uint32(n), C.byref(hs)))
+        return hid, t, u, v
+
+    def shade_step(self, o, d, tri_id, t, u, v, s0, s1):
+        """per-function device entry point (wpt_shade_step); all 1-D CUDA tensors, o/d 3-tuples"""
+        import torch
+        n = tri_id.numel()
+        dev = tri_id.device
+        no = [torch.zeros(n, device=dev) for _ in range(3)]
+        nd = [torch.zeros(n, device=dev) for _ in range(3)]
+        w = [torch.zeros(n, device=dev) for _ in range(3)]
+        arr = lambda ts: (C.c_void_p * 3)(*[t_.data_ptr() for t_ in ts])
+        _check(lib().wpt_shade_step(self._h, C.c_uint32(n), arr(o), arr(d), _ptr(tri_id), _ptr(t), _ptr(u), _ptr(v),
+                                    _ptr(s0), _ptr(s1), arr(no), arr(nd), arr(w), _stream_handle(None)))
+        return no, nd, w
+
+    def close(self):
+        if self._h:
+            lib().wpt_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Renderer:
+    """The sample/bounce loop of main() (src/main.cpp:385-429) as a wavefront pipeline."""
+
+    def __init__(self, scene, width, height, spp_per_pass=1):
+        self.scene = scene
+        self.width, self.height = width, height
+        self._h = C.c_void_p()
+        _check(lib().wpt_renderer_create(scene._h, C.c_int32(width), C.c_int32(height), C.c_int32(spp_per_pass),
+                                         C.byref(self._h)))
+
+    def set_profile(self, on):
+        _check(lib().wpt_renderer_set_profile(self._h, C.c_int(1 if on else 0)))
+
+    def set_tuning(self, trace_variant=0, ctas_per_sm=0, sort_rays=0):
+        _check(lib().wpt_renderer_set_tuning(self._h, C.c_int(trace_variant), C.c_int(ctas_per_sm), C.c_int(sort_rays)))
+
+    def _cfg(self, spp_begin, spp_count, depth, seed, tmin, tmax):
+        return RenderConfig(self.width, self.height, spp_begin, spp_count, depth, seed, tmin, tmax)
+
+    def render(self, camera, film, spp_begin, spp_count, depth, seed=0, tmin=1e-3, tmax=1e20, stream=None):
+        """film: CUDA float32 tensor [3, H*W] (planar, un-normalised sum is ADDED). Asynchronous."""
+        assert film.is_cuda and film.is_contiguous() and film.numel() == 3 * self.width * self.height
+        N = self.width * self.height
+        base = film.data_ptr()
+        cfg = self._cfg(spp_begin, spp_count, depth, seed, tmin, tmax)
+        _check(lib().wpt_render(self._h, C.byref(camera.c), C.byref(cfg), C.c_void_p(base), C.c_void_p(base + 4 * N),
+                                C.c_void_p(base + 8 * N), _stream_handle(stream)))
+
+    def finish(self, stream=None):
+        st = Stats()
+        _check(lib().wpt_render_finish(self._h, C.byref(st), _stream_handle(stream)))
+        return _stats_dict(st)
+
+    def render_host(self, camera, spp_begin, spp_count, depth, seed=0, tmin=1e-3, tmax=1e20, out=None):
+        """whole frame to HOST planar film [3, H*W], normalised by spp_count (src/main.cpp:369-439)."""
+        N = self.width * self.height
+        film = out if out is not None else np.empty((3, N), np.float32)
+        cfg = self._cfg(spp_begin, spp_count, depth, seed, tmin, tmax)
+        st = Stats()
+        _check(lib().wpt_render_host(self._h, C.byref(camera.c), C.byref(cfg), C.c_void_p(film[0].ctypes.data),
+                                     C.c_void_p(film[1].ctypes.data), C.c_void_p(film[2].ctypes.data), C.byref(st)))
+        return film, _stats_dict(st)
+
+    def close(self):
+        if self._h:
+            lib().wpt_renderer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _stats_dict(st):
+    d = {k: getattr(st, k) for k, _ in Stats._fields_ if k != "live"}
+    d["live"] = [int(x) for x in st.live]
+    return d
+
+
+def film_scale(film, scale, stream=None):
+    N = film.numel() // 3
+    base = film.data_ptr()
+    _check(lib().wpt_film_scale(C.c_void_p(base), C.c_void_p(base + 4 * N), C.c_void_p(base + 8 * N), C.c_uint32(N),
+                                C.c_float(scale), _stream_handle(stream)))
+
+
+def raygen(camera, width, height, spp_index, seed=0):
+    """wpt_raygen: camera rays of one global sample index for all pixels -> (o[3], d[3]) CUDA tensors"""
+    import torch
+    N = width * height
+    o = [torch.empty(N, device="cuda") for _ in range(3)]
+    d = [torch.empty(N, device="cuda") for _ in range(3)]
+    _check(lib().wpt_raygen(C.byref(camera.c), C.c_int32(width), C.c_int32(height), C.c_int32(spp_index),
+                            C.c_uint64(seed), *[_ptr(t) for t in o + d], _stream_handle(None)))
+    return o, d
+
+
+def philox(n, c1, c2, key):
+    import torch
+    out = torch.empty(4 * n, dtype=torch.int32, device="cuda")
+    _check(lib().wpt_philox(C.c_uint32(n), C.c_uint32(c1), C.c_uint32(c2), C.c_uint64(key), _ptr(out),
+                            _stream_handle(None)))
+    return out.view(n, 4)
+
+
+class Fimage:
+    """src/fimage.h:5-59"""
+
+    @staticmethod
+    def save_pfm(r, g, b, width, height, filepath):
+        r, g, b = (_np(x, np.float32).reshape(-1) for x in (r, g, b))
+        _check(lib().wpt_save_pfm(str(filepath).encode(), C.c_void_p(r.ctypes.data), C.c_void_p(g.ctypes.data),
+                                  C.c_void_p(b.ctypes.data), C.c_uint32(width), C.c_uint32(height)))
+
+
+def scene_from(sd, device=0):
+    """SceneData (scenes.py) -> committed Scene"""
+    s = Scene()
+    s.add_triangle_mesh(sd.pos, sd.idx, sd.nrm, sd.nidx, sd.mat, sd.albedo)
+    s.commit(device)
+    return s
+
+
+def camera_from(sd):
+    c = sd.camera
+    return ThinlensCamera(c["look_from"], c["look_at"], c["up"], 0.0, 1.0, c["fov_y"])

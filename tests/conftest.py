@@ -1,0 +1,50 @@
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "smallpt-enoki-optix_b200")
+for p in (ROOT, PKG, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def _have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def pytest_collection_modifyitems(config, items):
+    if _have_gpu():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
+@pytest.fixture(scope="session", autouse=True)
+def built():
+    """Make sure the oracle, the test-only host library and libwpt.so exist (built in-tree)."""
+    need = [os.path.join(ROOT, "oracle", "libwpt_oracle.so"), os.path.join(PKG, "libwpt.so"),
+            os.path.join(PKG, "libwpt_hosttest.so")]
+    if not all(os.path.exists(p) for p in need):
+        sys.path.insert(0, ROOT)
+        import __graft_entry__
+        __graft_entry__.build()
+    return True
+
+
+@pytest.fixture(scope="session")
+def hosttest():
+    import ctypes as C
+    return C.CDLL(os.path.join(PKG, "libwpt_hosttest.so"))

@@ -1,0 +1,325 @@
+"""-m gpu parity tests proper: the CUDA path through the C ABI (libwpt.so) against the CPU oracle
+and, where oracle/_ref is present, against the real Embree 3.6.1 of the reference tree."""
+import numpy as np
+import pytest
+
+import oracle_py as O
+import scenes
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+@pytest.fixture(scope="module")
+def cornell(torch_cuda):
+    import wpt
+    sd = scenes.cornell(50)
+    return sd, wpt.scene_from(sd), util.oracle_mesh(sd)
+
+
+def _dev_intersect(torch, scene, o, d, **kw):
+    ot = [torch.from_numpy(np.ascontiguousarray(o[:, k])).cuda() for k in range(3)]
+    dt = [torch.from_numpy(np.ascontiguousarray(d[:, k])).cuda() for k in range(3)]
+    out = scene.intersect(ot, dt, **kw)
+    torch.cuda.synchronize()
+    return tuple(x.cpu().numpy() for x in out)
+
+
+def test_minimal_kat(torch_cuda):
+    """Embree tutorials/minimal/minimal.cpp:72-213: unit triangle, hit at t=1 prim 0; second ray misses."""
+    import wpt
+    s = wpt.Scene()
+    s.add_triangle_mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]])
+    s.commit(0)
+    o = np.array([[0, 0, -1], [1, 1, -1]], np.float32)
+    d = np.array([[0, 0, 1], [0, 0, 1]], np.float32)
+    hid, t, u, v = _dev_intersect(torch_cuda, s, o, d, tmin=0.0, tmax=float("inf"))
+    assert hid.tolist() == [0, -1]
+    assert abs(t[0] - 1.0) < 1e-6 and u[0] == 0 and v[0] == 0
+    assert np.isnan(t[1])  # t,u,v untouched on miss
+
+
+def test_triangle_hit_kat(torch_cuda):
+    """Embree verify.cpp:2312-2399 TriangleHitTest: 256 rays from (0,0,-1) at the unit triangle:
+    u,v,t within 16 ulp of the analytic values."""
+    import wpt
+    s = wpt.Scene()
+    s.add_triangle_mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]])
+    s.commit(0)
+    g = np.arange(16, dtype=np.float32)
+    U, V = np.meshgrid(g, g, indexing="ij")
+    u0 = (U.reshape(-1) / 32.0 + 1 / 64.0).astype(np.float32)
+    v0 = (V.reshape(-1) / 32.0 + 1 / 64.0).astype(np.float32)
+    o = np.tile(np.array([[0, 0, -1]], np.float32), (256, 1))
+    d = np.stack([u0, v0, np.ones_like(u0)], 1).astype(np.float32)
+    hid, t, u, v = _dev_intersect(torch_cuda, s, o, d, tmin=0.0, tmax=float("inf"))
+    assert (hid == 0).all()
+    eps = 16 * np.finfo(np.float32).eps
+    assert np.abs(u - u0).max() <= eps and np.abs(v - v0).max() <= eps and np.abs(t - 1.0).max() <= eps
+
+
+@pytest.mark.parametrize("inside", [True, False])
+def test_intersect_vs_oracle_cornell(torch_cuda, cornell, inside):
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 400_000, seed=11 + inside, inside=inside)
+    got = _dev_intersect(torch_cuda, scene, o, d)
+    ref = om.intersect("bvh", o, d)
+    rate = util.compare_hits(ref, got, "cornell/oracle")
+    assert rate >= 0.9999
+    if O.ref_available():
+        util.compare_hits(om.intersect("embree", o, d), got, "cornell/embree")
+
+
+def test_intersect_mask_semantics(torch_cuda, cornell):
+    """wavefront_isect.cu:86-87: size-1 mask broadcasts, masked-out lanes are left untouched."""
+    torch = torch_cuda
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 10_000, seed=5)
+    full = _dev_intersect(torch, scene, o, d)
+    m = (np.arange(10_000) % 3 != 0).astype(np.uint8)
+    part = _dev_intersect(torch, scene, o, d, active=torch.from_numpy(m).cuda())
+    assert (part[0][m == 0] == -2).all() and np.isnan(part[1][m == 0]).all()
+    assert (part[0][m == 1] == full[0][m == 1]).all()
+    one = _dev_intersect(torch, scene, o, d, active=torch.ones(1, dtype=torch.uint8, device="cuda"))
+    assert (one[0] == full[0]).all()
+    zero = _dev_intersect(torch, scene, o, d, active=torch.zeros(1, dtype=torch.uint8, device="cuda"))
+    assert (zero[0] == -2).all()
+    bmask = _dev_intersect(torch, scene, o, d, active=torch.from_numpy(m.astype(bool)).cuda())
+    assert (bmask[0] == part[0]).all()
+
+
+def test_intersect_host_and_empty(torch_cuda, cornell):
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 5_000, seed=9)
+    a = scene.intersect_host(o, d)
+    b = _dev_intersect(torch_cuda, scene, o, d)
+    assert (a[0] == b[0]).all() and np.array_equal(a[1], b[1], equal_nan=True)
+    e = scene.intersect_host(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32))
+    assert e[0].size == 0
+
+
+def test_intersect_tmin_tmax(torch_cuda, cornell):
+    """tmin exclusive, tmax inclusive-ish window: results must equal the oracle's under the same window."""
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 100_000, seed=21)
+    for tmin, tmax in ((0.0, 0.5), (0.3, 1.0), (1e-3, 1e20)):
+        got = _dev_intersect(torch_cuda, scene, o, d, tmin=tmin, tmax=tmax)
+        ref = om.intersect("bvh", o, d, tmin=tmin, tmax=tmax)
+        util.compare_hits(ref, got, f"window {tmin},{tmax}")
+
+
+def test_intersect_knob_camera_and_bounce_rays(torch_cuda):
+    """C2-like scene: coherent camera rays and incoherent second-bounce rays vs oracle (+Embree)."""
+    import wpt
+    torch = torch_cuda
+    sd = scenes.knob(250, 100)
+    scene, om = wpt.scene_from(sd), util.oracle_mesh(sd)
+    cam = wpt.camera_from(sd)
+    W = H = 512
+    o_t, d_t = wpt.raygen(cam, W, H, 0, seed=7)
+    hit = scene.intersect(o_t, d_t)
+    torch.cuda.synchronize()
+    o = np.stack([x.cpu().numpy() for x in o_t], 1)
+    d = np.stack([x.cpu().numpy() for x in d_t], 1)
+    got = tuple(x.cpu().numpy() for x in hit)
+    ref = om.intersect("embree" if O.ref_available() else "bvh", o, d)
+    assert util.compare_hits(ref, got, "knob/camera") >= 0.9999
+    # bounce rays from the hit points
+    live = got[0] >= 0
+    n = int(live.sum())
+    s0 = torch.rand(n, device="cuda")
+    s1 = torch.rand(n, device="cuda")
+    idx = torch.from_numpy(np.nonzero(live)[0]).cuda()
+    sel = lambda ts: [t_[idx].contiguous() for t_ in ts]
+    no, nd, w = scene.shade_step(sel(o_t), sel(d_t), hit[0][idx].contiguous(), hit[1][idx].contiguous(),
+                                 hit[2][idx].contiguous(), hit[3][idx].contiguous(), s0, s1)
+    hit2 = scene.intersect(no, nd)
+    torch.cuda.synchronize()
+    o2 = np.stack([x.cpu().numpy() for x in no], 1)
+    d2 = np.stack([x.cpu().numpy() for x in nd], 1)
+    got2 = tuple(x.cpu().numpy() for x in hit2)
+    ref2 = om.intersect("embree" if O.ref_available() else "bvh", o2, d2)
+    assert util.compare_hits(ref2, got2, "knob/bounce") >= 0.9999
+
+
+def test_philox_kat(torch_cuda):
+    """Random123 known-answer vectors for philox4x32-10 + device == oracle on a sweep."""
+    import ctypes as C
+    import wpt
+    out = wpt.philox(1, 0, 0, 0).cpu().numpy().view(np.uint32)
+    assert [hex(x) for x in out[0]] == ["0x6627e8d5", "0xe169c58d", "0xbc57ac4c", "0x9b00dbd8"]
+    L = O.lib()
+    dev = wpt.philox(1000, 0xDEAD, 7, 0x0123456789ABCDEF).cpu().numpy().view(np.uint32)
+    for i in (0, 1, 17, 999):
+        ctr = (C.c_uint32 * 4)(i, 0xDEAD, 7, 0)
+        key = (C.c_uint32 * 2)(0x89ABCDEF, 0x01234567)
+        o = (C.c_uint32 * 4)()
+        L.orc_philox4x32_10(ctr, key, o)
+        assert list(o) == dev[i].tolist()
+
+
+def test_raygen_vs_oracle(torch_cuda):
+    """camera rays (src/pinhole.h:27-56) device vs oracle with the same Philox numbers: <= 1e-6 abs."""
+    import ctypes as C
+    import wpt
+    sd = scenes.cornell(8)
+    cam = wpt.camera_from(sd)
+    ocam = util.oracle_camera(sd)
+    W, H = 64, 48
+    o_t, d_t = wpt.raygen(cam, W, H, 3, seed=99)
+    d = np.stack([x.cpu().numpy() for x in d_t], 1)
+    o = np.stack([x.cpu().numpy() for x in o_t], 1)
+    L = O.lib()
+    for pix in (0, 1, 63, 64, 1000, W * H - 1):
+        ctr = (C.c_uint32 * 4)(pix, 3, 0, 0)
+        key = (C.c_uint32 * 2)(99, 0)
+        r = (C.c_uint32 * 4)()
+        L.orc_philox4x32_10(ctr, key, r)
+        xi = (C.c_float * 4)(*[L.orc_u32_to_f32(C.c_uint32(x)) for x in r])
+        po, pd = (C.c_float * 3)(), (C.c_float * 3)()
+        L.orc_camera_sample_pos(C.byref(ocam), xi, po)
+        xi2 = (C.c_float * 2)(xi[2], xi[3])
+        L.orc_camera_sample_dir(C.byref(ocam), C.c_int(pix % W), C.c_int(pix // W), po, C.c_int(W), C.c_int(H), xi2, pd)
+        assert np.abs(np.array(po) - o[pix]).max() <= 1e-6
+        assert np.abs(np.array(pd) - d[pix]).max() <= 2e-6
+
+
+def test_shade_step_vs_oracle(torch_cuda, cornell):
+    """one bounce (optix_backend.h:463-486 + main.cpp:414-424) device vs oracle on the same hits/uniforms"""
+    torch = torch_cuda
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 2000, seed=3)
+    hid, t, u, v = om.intersect("bvh", o, d)
+    live = np.nonzero(hid >= 0)[0][:500]
+    rng = np.random.default_rng(4)
+    s = rng.random((live.size, 2)).astype(np.float32)
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    no, nd, w = scene.shade_step([cu(o[live, k]) for k in range(3)], [cu(d[live, k]) for k in range(3)],
+                                 cu(hid[live]), cu(t[live]), cu(u[live]), cu(v[live]), cu(s[:, 0]), cu(s[:, 1]))
+    no = np.stack([x.cpu().numpy() for x in no], 1)
+    nd = np.stack([x.cpu().numpy() for x in nd], 1)
+    w = np.stack([x.cpu().numpy() for x in w], 1)
+    for k, i in enumerate(live):
+        ro, rd, rw = om.shade_step(o[i], d[i], hid[i], t[i], u[i], v[i], s[k])
+        assert np.abs(ro - no[k]).max() <= 1e-6 * max(1.0, np.abs(ro).max())
+        assert np.abs(rd - nd[k]).max() <= 2e-6
+        assert np.array_equal(rw, w[k])
+
+
+def _render_both(sd, W, H, spp, depth, seed, rng_mode, spp_per_pass=2):
+    import wpt
+    scene, om = wpt.scene_from(sd), util.oracle_mesh(sd)
+    cam, ocam = wpt.camera_from(sd), util.oracle_camera(sd)
+    r = wpt.Renderer(scene, W, H, spp_per_pass)
+    film, st = r.render_host(cam, 0, spp, depth, seed=seed)
+    ofilm, oseg = om.render("embree" if O.ref_available() else "bvh", ocam, W, H, 0, spp, depth, rng_mode=rng_mode, seed=seed)
+    return film, st, ofilm / spp, oseg
+
+
+def test_render_matches_oracle_same_rng(torch_cuda):
+    """C1 (configs[0]): 256x256, 4 spp, depth 5.  With the oracle driven by the same Philox counters the
+    two images must be the same paths: identical except where a ulp-level difference flipped a hit."""
+    sd = scenes.cornell(50, colored=True)
+    film, st, ofilm, oseg = _render_both(sd, 256, 256, 4, 5, seed=1234, rng_mode=O.RNG_PHILOX)
+    diff = np.abs(film - ofilm).max(0)
+    assert (diff > 1e-5).mean() < 0.01, f"{(diff > 1e-5).mean()} of pixels differ"
+    assert abs(film.mean() - ofilm.mean()) < 1e-3 * max(ofilm.mean(), 1e-6)
+    assert abs(st["segments"] - oseg) <= 1e-3 * oseg
+
+
+def test_render_three_sigma_vs_reference_rng(torch_cuda):
+    """north_star image bar: 3 sigma per pixel at equal spp against the oracle running the REFERENCE's
+    generator (per-pixel PCG32, main.cpp:376)."""
+    sd = scenes.cornell(50)
+    spp = 64
+    film, st, ofilm, oseg = _render_both(sd, 96, 96, spp, 5, seed=77, rng_mode=O.RNG_PCG32, spp_per_pass=8)
+    frac = util.three_sigma_outliers(film[0], ofilm[0], spp)
+    assert frac < 0.01, f"{frac} of pixels outside 3 sigma"
+    assert abs(film.mean() - ofilm.mean()) < 0.01 * ofilm.mean()
+    assert abs(st["segments"] - oseg) < 0.01 * oseg
+
+
+def test_render_spp_sharding_is_additive(torch_cuda):
+    """disjoint spp ranges with the global-index keyed RNG sum to the single-range render."""
+    import torch
+    import wpt
+    sd = scenes.cornell(16)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    W = H = 64
+    r = wpt.Renderer(scene, W, H, 4)
+    whole = torch.zeros(3, W * H, device="cuda")
+    r.render(cam, whole, 0, 8, 4, seed=5)
+    s_all = r.finish()
+    parts = torch.zeros(3, W * H, device="cuda")
+    r.render(cam, parts, 0, 3, 4, seed=5); s1 = r.finish()
+    r.render(cam, parts, 3, 5, 4, seed=5); s2 = r.finish()
+    assert torch.equal(whole, parts)          # albedo 1: sums of exact 0/1 contributions
+    assert s_all["segments"] == s1["segments"] + s2["segments"]
+    # spp_per_pass must not change the result either
+    r2 = wpt.Renderer(scene, W, H, 1)
+    one = torch.zeros(3, W * H, device="cuda")
+    r2.render(cam, one, 0, 8, 4, seed=5); r2.finish()
+    assert torch.equal(whole, one)
+
+
+def test_trace_variants_agree(torch_cuda):
+    import torch
+    import wpt
+    sd = scenes.cornell(16)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    W = H = 64
+    films = []
+    for variant in (0, 1, 2):
+        r = wpt.Renderer(scene, W, H, 2)
+        r.set_tuning(trace_variant=variant)
+        f = torch.zeros(3, W * H, device="cuda")
+        r.render(cam, f, 0, 4, 5, seed=3); r.finish()
+        films.append(f)
+    assert torch.equal(films[0], films[1]) and torch.equal(films[0], films[2])
+
+
+def test_sealed_room_is_black(torch_cuda):
+    """C5 semantics: no emitter — a sealed interior renders exactly 0; with the skylight > 0."""
+    import wpt
+    for sky, expect_zero in ((False, True), (True, False)):
+        sd = scenes.interior(33, 2, (16, 32), skylight=sky)
+        scene = wpt.scene_from(sd)
+        r = wpt.Renderer(scene, 64, 64, 4)
+        film, st = r.render_host(wpt.camera_from(sd), 0, 8, 6, seed=1)
+        assert (film.max() == 0.0) == expect_zero
+
+
+def test_pfm_roundtrip(tmp_path, torch_cuda):
+    import wpt
+    W, H = 5, 3
+    rng = np.random.default_rng(0)
+    r, g, b = (rng.random(W * H).astype(np.float32) for _ in range(3))
+    p = tmp_path / "x.pfm"
+    wpt.Fimage.save_pfm(r, g, b, W, H, p)
+    raw = p.read_bytes()
+    head = b"PF\n5 3\n-1\n"
+    assert raw.startswith(head)
+    data = np.frombuffer(raw[len(head):], np.float32).reshape(H, W, 3)
+    assert np.array_equal(data[::-1, :, 0].reshape(-1), r)      # rows bottom-up (fimage.h:49)
+    assert np.array_equal(data[::-1, :, 2].reshape(-1), b)
+
+
+def test_errors(torch_cuda):
+    import wpt
+    s = wpt.Scene()
+    with pytest.raises(wpt.WptError):
+        s.commit(0)
+    with pytest.raises(wpt.WptError):
+        s.add_triangle_mesh(np.zeros((0, 3)), np.zeros((0, 3)))
+    s.add_triangle_mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 5]])
+    with pytest.raises(wpt.WptError):
+        s.commit(0)           # index out of range is caught by the builder
