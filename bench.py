@@ -189,13 +189,13 @@ def run_ours(args):
     r = wpt.Renderer(scene, W, H, args.spp_per_pass)
     r.set_tuning(args.variant, args.ctas_per_sm, 0)
     film = torch.zeros(3, N, device="cuda")
-    spp_begin = rank * spp            # disjoint, decorrelated spp ranges (RNG keyed on the global index)
+    import wpt_dist as wdist
+    spp_begin, _ = wdist.spp_range_weak(rank, world, spp)   # disjoint, decorrelated (RNG keyed on global index)
 
     def step():
         film.zero_()
         r.render(cam, film, spp_begin, spp, depth, seed=SEED)
-        if world > 1:
-            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)      # one NCCL reduce of the partial films
+        wdist.reduce_film(film, dst=0)                          # one NCCL reduce of the partial films
         wpt.film_scale(film, 1.0 / (spp * world))
         return r.finish()
 

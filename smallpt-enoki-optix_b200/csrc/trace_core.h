@@ -38,10 +38,14 @@ WPT_HD uint32_t f2u(float f)
     uint32_t u; memcpy(&u, &f, 4); return u;
 #endif
 }
+// PTX prmt.b32, default mode: selector nibble bits 2:0 pick a byte of {b,a}, bit 3 replicates that
+// byte's sign bit instead.  (__byte_perm ignores bit 3, so the sign mode needs the PTX form.)
 WPT_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t sel)
 {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(a, b, sel);
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
 #else
     const uint64_t src = ((uint64_t)b << 32) | a;
     uint32_t r = 0;

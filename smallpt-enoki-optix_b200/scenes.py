@@ -214,7 +214,7 @@ def interior(grid=289, n_pillars=8, pillar_grid=(64, 128), skylight=True, grey=0
     into the ceiling."""
     b = _Builder()
     L = 4.0
-    t = np.linspace(-L, L, grid)
+    t = np.linspace(-L - 0.25, L + 0.25, grid)      # walls overlap at the edges: bumps (< 0.1) cannot open a seam
     A, B = np.meshgrid(t, t, indexing="ij")
     bump = 0.06 * np.sin(3.1 * A) * np.cos(2.7 * B) + 0.03 * np.sin(7.3 * A + 0.4) * np.sin(6.1 * B)
 

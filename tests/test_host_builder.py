@@ -1,0 +1,100 @@
+"""CPU checks of the product's host code: the SAH BVH8 builder's structure and the
+__host__ __device__ traversal core compiled for the CPU (test-only library) against the oracle."""
+import numpy as np
+import pytest
+
+import oracle_py as O
+import scenes
+import util
+
+
+def _sd(pos, idx):
+    pos = np.asarray(pos, np.float32).reshape(-1, 3)
+    idx = np.asarray(idx, np.int32).reshape(-1, 3)
+    return scenes.SceneData("t", pos, idx, np.zeros((1, 3)), np.zeros_like(idx), np.zeros(len(idx)), [[1, 1, 1]], {})
+
+
+SCENES = {
+    "cornell": lambda: scenes.cornell(20),
+    "knob": lambda: scenes.knob(100, 40),
+    "terrain": lambda: scenes.terrain_spheres(41, 4, 8),
+    "interior": lambda: scenes.interior(33, 2, (16, 32)),
+}
+
+
+@pytest.mark.parametrize("name", list(SCENES))
+def test_builder_structure(hosttest, name):
+    """every triangle referenced exactly once; every quantised child box contains its subtree"""
+    sd = SCENES[name]()
+    rc, st = util.hosttest_build(hosttest, sd)
+    assert rc == 0 and st["problems"] == 0
+    assert st["n_tris"] == sd.n_tris and st["max_depth"] <= 31
+    assert st["n_nodes"] < sd.n_tris  # wide nodes: far fewer than triangles
+
+
+@pytest.mark.parametrize("name", list(SCENES))
+def test_host_traversal_vs_oracle(hosttest, name):
+    sd = SCENES[name]()
+    om = util.oracle_mesh(sd)
+    for inside in (True, False):
+        o, d = util.random_rays(sd, 60_000, seed=7, inside=inside)
+        got = util.hosttest_trace(hosttest, sd, o, d)
+        ref = om.intersect("bvh", o, d)
+        assert util.compare_hits(ref, got, name) >= 0.9999
+
+
+def test_degenerate_inputs(hosttest):
+    rng = np.random.default_rng(0)
+    # one triangle, two triangles, many coincident triangles, a flat axis-aligned grid, huge + tiny mix
+    one = _sd([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]])
+    dup = _sd([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 2]] * 37)
+    g = np.stack(np.meshgrid(np.arange(12.0), np.arange(12.0), indexing="ij"), -1).reshape(-1, 2)
+    flat_pos = np.concatenate([g[:, :1], np.zeros((len(g), 1)), g[:, 1:]], 1)
+    ii, jj = np.meshgrid(np.arange(11), np.arange(11), indexing="ij")
+    a = (ii * 12 + jj).reshape(-1)
+    flat = _sd(flat_pos, np.concatenate([np.stack([a, a + 12, a + 13], 1), np.stack([a, a + 13, a + 1], 1)]))
+    c = rng.uniform(-1, 1, (300, 1, 3))
+    small = (c + rng.normal(0, 1e-4, (300, 3, 3))).reshape(-1, 3)
+    big = np.array([[-50, -2, -50], [50, -2, -50], [0, -2, 80]])
+    mix = _sd(np.concatenate([small, big]), np.concatenate([np.arange(900).reshape(-1, 3), [[900, 901, 902]]]))
+    for sd in (one, dup, flat, mix):
+        rc, st = util.hosttest_build(hosttest, sd)
+        assert rc == 0 and st["problems"] == 0, st
+        om = util.oracle_mesh(sd)
+        o, d = util.random_rays(sd, 20_000, seed=3, inside=False)
+        d[:5000] = [0, -1, 0]            # axis-aligned rays (zero direction components)
+        o[:5000, 1] = 5.0
+        got = util.hosttest_trace(hosttest, sd, o, d)
+        ref = om.intersect("brute" if sd.n_tris < 400 else "bvh", o, d)
+        if sd is dup:   # 37 coincident triangles: every hit is a documented t-tie; only t must agree
+            assert ((ref[0] >= 0) == (got[0] >= 0)).all()
+            h = ref[0] >= 0
+            assert np.allclose(ref[1][h], got[1][h], rtol=1e-6)
+        else:
+            assert util.compare_hits(ref, got, "degenerate") >= 0.9999
+
+
+def test_near_tmin_hits_are_not_culled(hosttest):
+    """regression: a hit at t = tmin*(1+eps) on a huge ground quad at the scene's lower bound"""
+    sd = scenes.knob(60, 24)
+    om = util.oracle_mesh(sd)
+    rng = np.random.default_rng(5)
+    n = 50_000
+    o = np.stack([rng.uniform(-5, 5, n), np.full(n, -1.3) + rng.uniform(0.00100001, 0.00102, n) * 0.8,
+                  rng.uniform(-5, 5, n)], 1).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d[:, 1] = -np.abs(d[:, 1]) - 0.5
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    got = util.hosttest_trace(hosttest, sd, o, d)
+    ref = om.intersect("bvh", o, d)
+    assert util.compare_hits(ref, got, "near-tmin") >= 0.9999
+
+
+def test_config_triangle_counts():
+    assert scenes.cornell(50).n_tris == 19_610
+    assert scenes.knob(500, 200).n_tris == 200_002        # C2
+    sd = scenes.terrain_spheres()
+    assert sd.n_tris == 1_007_232                         # C3
+    assert np.isfinite(sd.pos).all() and np.abs(sd.pos).max() <= 10.0
+    ln = np.linalg.norm(sd.nrm, axis=1)
+    assert np.abs(ln - 1).max() < 1e-4
