@@ -288,14 +288,24 @@ def test_trace_variants_agree(torch_cuda):
 
 
 def test_sealed_room_is_black(torch_cuda):
-    """C5 semantics: no emitter — a sealed interior renders exactly 0; with the skylight > 0."""
+    """C5 semantics: no emitter — light only enters through escaping rays.  A sealed
+    interior is black except for the reference's own leaks (the bounce is sampled about the
+    interpolated SHADING normal with no offset, main.cpp:414-424, so on a coarsely tessellated bumpy
+    wall a direction can dip under the geometric surface): the device image must equal the oracle's
+    path for path, the sealed room must be >= 10x darker than the one with the skylight."""
     import wpt
-    for sky, expect_zero in ((False, True), (True, False)):
+    means = []
+    for sky in (False, True):
         sd = scenes.interior(33, 2, (16, 32), skylight=sky)
         scene = wpt.scene_from(sd)
         r = wpt.Renderer(scene, 64, 64, 4)
         film, st = r.render_host(wpt.camera_from(sd), 0, 8, 6, seed=1)
-        assert (film.max() == 0.0) == expect_zero
+        ofilm, oseg = util.oracle_mesh(sd).render("bvh", util.oracle_camera(sd), 64, 64, 0, 8, 6,
+                                                  rng_mode=O.RNG_PHILOX, seed=1)
+        assert (np.abs(film - ofilm / 8).max(0) > 1e-5).mean() < 0.01
+        assert abs(st["segments"] - oseg) <= 2e-3 * oseg
+        means.append(float(film.mean()))
+    assert means[1] > 0 and means[0] < 0.1 * means[1], means
 
 
 def test_pfm_roundtrip(tmp_path, torch_cuda):
