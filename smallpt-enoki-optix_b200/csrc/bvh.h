@@ -1,28 +1,32 @@
 // bvh.h — the flattened acceleration structure shared by the host builder and the device kernels.
 //
 // Replaces the OptiX GAS the reference builds in OptixBackend::set_triangles_soup
-// (src/accel/optix_backend.h:283-364).  Layout: 8-wide nodes with children quantised to 8 bits
+// (src/accel/optix_backend.h:283-364).  Layout: 8-wide nodes whose child boxes are quantised
 // against a per-node origin and per-axis power-of-two scale (compressed wide BVH in the style of
-// Ylitie, Karras, Laine, HPG 2017), 80 bytes = five 16-byte loads; triangles as 48-byte blocks
-// (v0, e1 = v0-v1, e2 = v2-v0, Ng = cross(e2,e1): the operands of Embree's Moeller-Trumbore test,
-// dependencies/embree/kernels/geometry/triangle.h:54, triangle_intersector_moeller.h:75-113).
+// Ylitie, Karras, Laine, HPG 2017), but with the planes stored as bfloat16 PAIRS instead of bytes:
+// one node is exactly one 128-byte cache line = eight 16-byte loads, and decoding a plane costs no
+// ALU-pipe instruction on sm_100a (see trace_core.h: the odd child of a pair is used as a float as
+// it lies in the register, the even child is one IMAD.SHL on the FMA pipe).  Triangles are 48-byte
+// blocks (v0, e1 = v0-v1, e2 = v2-v0, Ng = cross(e2,e1): the operands of Embree's Moeller-Trumbore
+// test, dependencies/embree/kernels/geometry/triangle.h:54, triangle_intersector_moeller.h:75-113).
 #pragma once
 #include <stdint.h>
 #include <vector_types.h>
 
 namespace wpt {
 
-struct alignas(16) Node8 {
-    float    p[3];        // quantisation origin (node lower corner)
+// planes[axis][side][j]: side 0 = lower planes, 1 = upper planes; word j holds child 2j in its low
+// half and child 2j+1 in its high half, each a bfloat16 in quantisation units q: plane = p + q*2^(e-127).
+struct alignas(128) Node8 {
+    float    p[3];        // quantisation origin (slightly below the node's lower corner)
     uint8_t  e[3];        // biased exponents: scale_k = 2^(e[k]-127)
     uint8_t  imask;       // bit i set: slot i holds an internal child
     uint32_t child_base;  // index of the first internal child (children are contiguous, slot order)
     uint32_t tri_base;    // index of the first triangle block of this node's leaf children
-    uint8_t  meta[8];     // 0 = empty; internal: 0x20 | (24+slot); leaf: unary count<<5 | tri offset
-    uint8_t  qlo[3][8];   // quantised lower bounds, [axis][slot]
-    uint8_t  qhi[3][8];   // quantised upper bounds
+    uint8_t  meta[8];     // 0 = empty; internal: 0xff; leaf: count<<5 | tri offset (count 1..3, offset 0..23)
+    uint32_t planes[3][2][4];
 };
-static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
+static_assert(sizeof(Node8) == 128, "Node8 must be 128 bytes");
 
 struct alignas(16) Tri48 {
     float v0[3], e1[3], e2[3], ng[3];
@@ -44,7 +48,7 @@ constexpr int kStackSize = 32;   // traversal stack entries (one per tree level 
 
 // device-side view (all pointers device memory)
 struct BvhView {
-    const uint4 *nodes;     // Node8 as 5 x uint4
+    const uint4 *nodes;     // Node8 as 8 x uint4
     const float4 *tris;     // Tri48 as 3 x float4
     const int32_t *prim_id; // leaf slot -> original triangle index
     uint32_t n_nodes, n_tris;

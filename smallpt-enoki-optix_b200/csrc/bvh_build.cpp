@@ -219,12 +219,57 @@ inline uint8_t exp_for_extent(float extent, float maxabs)
 
 }  // namespace
 
+// ---- bfloat16 plane encoding (see bvh.h / trace_core.h) -------------------------------------------
+namespace {
+inline float bits_to_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline uint32_t float_to_bits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+// largest bfloat16 <= x, x >= 0
+inline uint16_t bf16_floor_pos(double x)
+{
+    if (!(x > 0.0)) return 0;
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafterf(f, -kInf);
+    return (uint16_t)(float_to_bits(f) >> 16);   // truncation = floor for positive values
+}
+// what the device sees for a plane stored in the HIGH half of a word whose low half is `low`
+inline double decode_high(uint16_t stored, uint16_t low) { return (double)bits_to_float(((uint32_t)stored << 16) | low); }
+inline double decode_low(uint16_t stored) { return (double)bits_to_float((uint32_t)stored << 16); }
+
+// lower plane: the largest encodable value whose DECODED value is <= x
+inline uint16_t enc_lo(double x, bool high_half, uint16_t low)
+{
+    uint16_t s = bf16_floor_pos(x);
+    if (!high_half) return s;
+    while (s > 0 && decode_high(s, low) > x) s--;
+    if (s == 0 && decode_high(0, low) > x) return 0x8000u;   // -0 | garbage = a tiny negative number
+    return s;
+}
+// upper plane: the smallest encodable value whose decoded value is >= x
+inline uint16_t enc_hi(double x, bool high_half, uint16_t low)
+{
+    uint16_t s = bf16_floor_pos(x);
+    while ((high_half ? decode_high(s, low) : decode_low(s)) < x) s++;
+    return s;
+}
+constexpr uint16_t kEmptyLo = 0x4680u;  // +16384: an inverted box, never hit
+constexpr uint16_t kEmptyHi = 0xC680u;  // -16384
+}  // namespace
+
+// conservative world-space box the traversal kernel effectively tests for child `slot`
 void node_child_bounds(const Node8 &n, int slot, float lo[3], float hi[3])
 {
+    const int j = slot >> 1;
+    const bool high = slot & 1;
     for (int k = 0; k < 3; k++) {
         const double s = std::ldexp(1.0, (int)n.e[k] - 127);
-        lo[k] = (float)((double)n.p[k] + s * n.qlo[k][slot]);
-        hi[k] = (float)((double)n.p[k] + s * n.qhi[k][slot]);
+        const uint32_t wl = n.planes[k][0][j], wh = n.planes[k][1][j];
+        const double ql = high ? (double)bits_to_float(wl) : decode_low((uint16_t)(wl & 0xffffu));
+        const double qh = high ? (double)bits_to_float(wh) : decode_low((uint16_t)(wh & 0xffffu));
+        lo[k] = (float)((double)n.p[k] + s * ql);
+        hi[k] = (float)((double)n.p[k] + s * qh);
+        // the float conversions above round to nearest: push outwards so the check stays strict
+        if ((double)lo[k] < (double)n.p[k] + s * ql) lo[k] = std::nextafterf(lo[k], kInf);
+        if ((double)hi[k] > (double)n.p[k] + s * qh) hi[k] = std::nextafterf(hi[k], -kInf);
     }
 }
 
@@ -369,18 +414,35 @@ bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets,
         node.child_base = (uint32_t)out.nodes.size();
         node.tri_base = (uint32_t)out.tris.size();
         uint32_t tri_off = 0;
+        uint16_t qlo[3][8], qhi[3][8];
+        for (int s = 0; s < 8; s++)
+            for (int k = 0; k < 3; k++) { qlo[k][s] = kEmptyLo; qhi[k][s] = kEmptyHi; }
+        // even slots first: the odd child of a pair is rounded against the bits its sibling leaves
+        // in the low half of the shared word
+        for (int pass = 0; pass < 2; pass++) {
+            for (int s = pass; s < 8; s += 2) {
+                const int c = child_in_slot[s];
+                if (c < 0) continue;
+                const Node2 &cn = n2[kids[c]];
+                for (int k = 0; k < 3; k++) {
+                    const double sc = std::ldexp(1.0, (int)node.e[k] - 127);
+                    const double xl = ((double)cn.b.lo[k] - (double)node.p[k]) / sc - 1.0 / 64.0;
+                    const double xh = ((double)cn.b.hi[k] - (double)node.p[k]) / sc + 1.0 / 64.0;
+                    qlo[k][s] = enc_lo(xl, pass == 1, qlo[k][s & ~1]);
+                    qhi[k][s] = enc_hi(xh, pass == 1, qhi[k][s & ~1]);
+                }
+            }
+        }
+        for (int k = 0; k < 3; k++)
+            for (int j = 0; j < 4; j++) {
+                node.planes[k][0][j] = (uint32_t)qlo[k][2 * j] | ((uint32_t)qlo[k][2 * j + 1] << 16);
+                node.planes[k][1][j] = (uint32_t)qhi[k][2 * j] | ((uint32_t)qhi[k][2 * j + 1] << 16);
+            }
         for (int s = 0; s < 8; s++) {
             const int c = child_in_slot[s];
             if (c < 0) continue;
             const uint32_t v = kids[c];
             const Node2 &cn = n2[v];
-            for (int k = 0; k < 3; k++) {
-                const double sc = std::ldexp(1.0, (int)node.e[k] - 127);
-                double ql = std::floor(((double)cn.b.lo[k] - (double)node.p[k]) / sc - 1.0 / 64.0);
-                double qh = std::ceil(((double)cn.b.hi[k] - (double)node.p[k]) / sc + 1.0 / 64.0);
-                node.qlo[k][s] = (uint8_t)std::max(0.0, std::min(255.0, ql));
-                node.qhi[k][s] = (uint8_t)std::max(0.0, std::min(255.0, qh));
-            }
             if (col.is_leaf(v)) {
                 const uint32_t cnt = cn.count;
                 node.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | tri_off);
@@ -398,7 +460,7 @@ bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets,
                 tri_off += cnt;
                 sah += (double)(cn.b.half_area() / root_area) * kCostTri * cnt;
             } else {
-                node.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
+                node.meta[s] = 0xffu;
                 node.imask |= (uint8_t)(1u << s);
                 out.nodes.emplace_back();
                 queue.push_back({v, w.depth + 1});

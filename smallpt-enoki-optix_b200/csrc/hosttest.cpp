@@ -73,10 +73,11 @@ int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uin
     return 0;
 }
 
-int wpt_hosttest_trace(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
-                       const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
-                       const float *dz, float tmin, float tmax, uint32_t n,
-                       int32_t *id, float *t, float *u, float *v)
+// counters (optional): [0] node visits, [1] triangle tests, summed over all rays
+int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
+                             const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
+                             const float *dz, float tmin, float tmax, uint32_t n,
+                             int32_t *id, float *t, float *u, float *v, double *counters)
 {
     BuiltBvh b;
     const char *err = nullptr;
@@ -87,14 +88,26 @@ int wpt_hosttest_trace(const float *pos, uint32_t n_pos, const int32_t *idx, uin
     view.prim_id = b.prim_id.data();
     view.n_nodes = (uint32_t)b.nodes.size();
     view.n_tris = (uint32_t)b.tris.size();
-#pragma omp parallel for schedule(dynamic, 1024)
+    uint64_t nodes_visited = 0, tris_tested = 0;
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : nodes_visited, tris_tested)
     for (int64_t i = 0; i < (int64_t)n; i++) {
         const RayCtx r = make_ray(ox[i], oy[i], oz[i], dx[i], dy[i], dz[i], tmin);
         LocalStack st;
-        const Hit h = trace_ray(view, r, tmax, st);
+        uint64_t c[2] = {0, 0};
+        const Hit h = trace_ray(view, r, tmax, st, c);
+        nodes_visited += c[0]; tris_tested += c[1];
         id[i] = h.slot < 0 ? -1 : view.prim_id[h.slot];
         if (h.slot >= 0) { t[i] = h.t; u[i] = h.u; v[i] = h.v; }
     }
+    if (counters) { counters[0] = (double)nodes_visited; counters[1] = (double)tris_tested; }
     return 0;
+}
+
+int wpt_hosttest_trace(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
+                       const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
+                       const float *dz, float tmin, float tmax, uint32_t n,
+                       int32_t *id, float *t, float *u, float *v)
+{
+    return wpt_hosttest_trace_stats(pos, n_pos, idx, n_tris, ox, oy, oz, dx, dy, dz, tmin, tmax, n, id, t, u, v, nullptr);
 }
 }

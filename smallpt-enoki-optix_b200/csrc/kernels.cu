@@ -69,6 +69,9 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
                  uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
 {
     __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+    __shared__ uint8_t perm_lut[8 * 256];   // perm_lut[o*256 + m] = perm8(m, o): visiting priority of slot mask m
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += kTraceBlock) perm_lut[i] = (uint8_t)perm8(i & 255u, i >> 8);
+    __syncthreads();
     const uint32_t n = n_ptr ? *n_ptr : n_static;
     if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
     const unsigned lane = threadIdx.x & 31u;
@@ -77,7 +80,8 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
     int sp = 0;
 
     bool active = false, exhausted = false;
-    uint32_t ray_i = 0, oct_inv = 0;
+    uint32_t ray_i = 0;
+    const uint8_t *lut = perm_lut;
     RayCtx r;
     Hit hit;
     uint2 G;
@@ -85,77 +89,76 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
     hit.slot = -1; hit.t = hit.u = hit.v = 0.0f;
 
     for (;;) {
-        // ---- refill idle lanes: one warp-aggregated atomic on the global cursor
-        const unsigned idle = __ballot_sync(0xffffffffu, !active);
-        if (idle && !exhausted) {
-            const int cnt = __popc(idle);
-            const int leader = __ffs(idle) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)cnt);
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (base + (uint32_t)cnt >= n) exhausted = true;
-            if (!active) {
-                const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                float ox, oy, oz, dx, dy, dz, t0, t1;
-                if (i < n && io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) {
-                    r = make_ray(ox, oy, oz, dx, dy, dz, t0);
-                    oct_inv = r.oct_inv4 & 7u;
-                    hit.slot = -1; hit.t = t1; hit.u = hit.v = 0.0f;
-                    G.x = 0u; G.y = 0x80000000u;
-                    sp = 0;
-                    ray_i = i;
-                    active = true;
+        // ---- refill idle lanes once too few of the warp are working: one warp-aggregated atomic on
+        // the global cursor.  Single flat loop: every iteration is one node step of every active lane.
+        const unsigned act = __ballot_sync(0xffffffffu, active);
+        if (__popc(act) < (FETCH_THRESHOLD > 0 ? FETCH_THRESHOLD : 1)) {
+            if (!exhausted) {
+                const unsigned idle = ~act;
+                const int cnt = __popc(idle);
+                const int leader = __ffs(idle) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)cnt);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (base + (uint32_t)cnt >= n) exhausted = true;
+                if (!active) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                    float ox, oy, oz, dx, dy, dz, t0, t1;
+                    if (i < n && io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) {
+                        r = make_ray(ox, oy, oz, dx, dy, dz, t0);
+                        lut = perm_lut + r.oct_inv * 256u;
+                        hit.slot = -1; hit.t = t1; hit.u = hit.v = 0.0f;
+                        G.x = 0u; G.y = 0x01000000u;
+                        sp = 0;
+                        ray_i = i;
+                        active = true;
+                    }
                 }
+                if (!__any_sync(0xffffffffu, active)) {
+                    if (exhausted) break;
+                    continue;
+                }
+            } else if (act == 0u) {
+                break;
             }
         }
-        if (!__any_sync(0xffffffffu, active)) {
-            if (exhausted) break;
-            continue;
-        }
-
-        // ---- traverse until done, or until too few lanes of the warp are still working
-        while (active) {
-            uint2 T;
-            T.x = T.y = 0u;
-            if (G.y & 0xff000000u) {
-                const int bit = 31 - __clz((int)G.y);
-                G.y &= ~(1u << bit);
-                if (G.y & 0xff000000u) {
-                    if (sp < kSmemStack) my[sp * kTraceBlock] = G; else lstack[sp - kSmemStack] = G;
-                    sp++;
-                }
-                const uint32_t slot = ((uint32_t)bit - 24u) ^ oct_inv;
-                const uint32_t rel = (uint32_t)__popc(G.y & ~(0xffffffffu << slot) & 0xffu);
-                const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 5;
-                const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
-                            n4 = __ldg(np + 4);
-                const uint32_t hm = node_hits(n0, n1, n2, n3, n4, r, hit.t);
-                G.x = n1.x; G.y = (hm & 0xff000000u) | (n0.w >> 24);
-                T.x = n1.y; T.y = hm & 0x00ffffffu;
-            } else {
-                T = G; G.x = G.y = 0u;
+        if (active) {
+            // next internal child, front to back: highest pending priority bit
+            const int bit = 31 - __clz((int)G.y);
+            G.y ^= 1u << bit;
+            if (G.y >> 24) {
+                if (sp < kSmemStack) my[sp * kTraceBlock] = G; else lstack[sp - kSmemStack] = G;
+                sp++;
             }
-            while (T.y) {
-                const int bit = 31 - __clz((int)T.y);
-                T.y &= ~(1u << bit);
-                const uint32_t ti = T.x + (uint32_t)bit;
+            const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
+            const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
+            const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 8;
+            uint4 n0, n1, qxl, qxh, qyl, qyh, qzl, qzh;
+            ld_node2(np, n0, n1); ld_node2(np + 2, qxl, qxh); ld_node2(np + 4, qyl, qyh); ld_node2(np + 6, qzl, qzh);
+            const uint32_t h8 = node_hits8(n0, qxl, qxh, qyl, qyh, qzl, qzh, r, hit.t);
+            const uint32_t imask = n0.w >> 24;
+            G.x = n1.x;
+            G.y = ((uint32_t)lut[h8 & imask] << 24) | imask;
+            uint32_t T = leaf_tri_mask(h8 & ~imask, n1.z, n1.w);
+            while (T) {
+                const int tb = 31 - __clz((int)T);
+                T ^= 1u << tb;
+                const uint32_t ti = n1.y + (uint32_t)tb;
                 const float4 *tp = bvh.tris + (size_t)ti * 3;
                 const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
                 if (tri_hit(t0, t1, t2, r, hit.t, hit.u, hit.v)) hit.slot = (int32_t)ti;
             }
-            if (!(G.y & 0xff000000u)) {
+            if (!(G.y >> 24)) {
                 if (sp == 0) {
                     const int32_t prim = hit.slot < 0 ? -1 : __ldg(bvh.prim_id + hit.slot);
                     io.store(ray_i, prim, hit.t, hit.u, hit.v);
                     active = false;
-                    break;
+                } else {
+                    sp--;
+                    G = sp < kSmemStack ? my[sp * kTraceBlock] : lstack[sp - kSmemStack];
                 }
-                sp--;
-                G = sp < kSmemStack ? my[sp * kTraceBlock] : lstack[sp - kSmemStack];
             }
-            if (FETCH_THRESHOLD > 0 && __popc(__activemask()) < FETCH_THRESHOLD) break;
         }
-        __syncwarp();
     }
 }
 

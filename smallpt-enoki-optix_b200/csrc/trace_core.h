@@ -7,6 +7,13 @@
 // Triangle test: accept rules and operation order of Embree's Moeller-Trumbore intersector
 // (dependencies/embree/kernels/geometry/triangle_intersector_moeller.h:75-113): den != 0, U >= 0,
 // V >= 0, U+V <= |den|, |den|*tnear < T <= |den|*tfar.
+//
+// Instruction budget of the node test (sm_100a: the ALU pipe — PRMT/LOP3/SHF/SEL/FMNMX/FSETP —
+// issues at half the rate of the FMA pipe — FFMA/FMUL/IMAD — so ALU-pipe instructions are what is
+// minimised): per child 6 FFMA, 2 FMNMX3, 2 FMNMX, 1 FSET, 1 FFMA (mask accumulate); per child PAIR
+// 6 SEL (near/far by ray sign) and 6 IMAD.SHL (even child's planes); the odd child's planes are used
+// as floats as loaded (their low 16 bits are the sibling's plane: the builder rounds so that the
+// perturbation is conservative).
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -38,26 +45,6 @@ WPT_HD uint32_t f2u(float f)
     uint32_t u; memcpy(&u, &f, 4); return u;
 #endif
 }
-// PTX prmt.b32, default mode: selector nibble bits 2:0 pick a byte of {b,a}, bit 3 replicates that
-// byte's sign bit instead.  (__byte_perm ignores bit 3, so the sign mode needs the PTX form.)
-WPT_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t sel)
-{
-#if defined(__CUDA_ARCH__)
-    uint32_t r;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
-    return r;
-#else
-    const uint64_t src = ((uint64_t)b << 32) | a;
-    uint32_t r = 0;
-    for (int i = 0; i < 4; i++) {
-        const uint32_t n = (sel >> (4 * i)) & 0xf;
-        uint32_t byte = (uint32_t)(src >> (8 * (n & 7))) & 0xff;
-        if (n & 8) byte = (byte & 0x80) ? 0xff : 0x00;
-        r |= byte << (8 * i);
-    }
-    return r;
-#endif
-}
 WPT_HD int high_bit(uint32_t x)  // index of the highest set bit, x != 0
 {
 #if defined(__CUDA_ARCH__)
@@ -74,13 +61,24 @@ WPT_HD int pop_count(uint32_t x)
     return __builtin_popcount(x);
 #endif
 }
-
-// float with bits 0x4380qq00 = 256 + q/128: one PRMT turns a quantised byte into an FMA operand
-// (no I2F).  t = f*A + B with A = 128*scale/d and B = (p-o)/d - 256*A gives (p + q*scale - o)/d.
-template <int J>
-WPT_HD float q2f(uint32_t word)
+// byte `i` (0..7) of the 64-bit value {hi,lo}
+WPT_HD uint32_t byte_of(uint32_t lo, uint32_t hi, uint32_t i)
 {
-    return u2f(byte_perm(word, 0x43800000u, 0x7604u | (J << 4)));
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(lo, hi, i) & 0xffu;
+#else
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> (8 * i)) & 0xffu;
+#endif
+}
+// permutation of the bit positions of an 8-bit mask by XOR with o: result bit (s ^ o) = m bit s.
+// Internal children are visited in order of decreasing (slot ^ oct_inv) — slot s holds the child
+// lying furthest towards corner s of the node, so that is front to back for the ray's octant.
+WPT_HD uint32_t perm8(uint32_t m, uint32_t o)
+{
+    if (o & 1u) m = ((m & 0x55u) << 1) | ((m >> 1) & 0x55u);
+    if (o & 2u) m = ((m & 0x33u) << 2) | ((m >> 2) & 0x33u);
+    if (o & 4u) m = ((m & 0x0fu) << 4) | ((m >> 4) & 0x0fu);
+    return m;
 }
 
 // ---------------------------------------------------------------- ray
@@ -88,7 +86,7 @@ struct RayCtx {
     float ox, oy, oz, dx, dy, dz;
     float ix, iy, iz;     // reciprocal direction (zero components replaced by +-1e-30 first)
     float tmin;
-    uint32_t oct_inv4;    // (dx>=0 | dy>=0<<1 | dz>=0<<2) replicated into four bytes
+    uint32_t oct_inv;     // dx>=0 | dy>=0<<1 | dz>=0<<2
 };
 
 WPT_HD RayCtx make_ray(float ox, float oy, float oz, float dx, float dy, float dz, float tmin)
@@ -100,60 +98,67 @@ WPT_HD RayCtx make_ray(float ox, float oy, float oz, float dx, float dy, float d
     const float sy = fabsf(dy) > eps ? dy : copysignf(eps, dy);
     const float sz = fabsf(dz) > eps ? dz : copysignf(eps, dz);
     r.ix = 1.0f / sx; r.iy = 1.0f / sy; r.iz = 1.0f / sz;
-    const uint32_t oi = (sx >= 0.0f ? 1u : 0u) | (sy >= 0.0f ? 2u : 0u) | (sz >= 0.0f ? 4u : 0u);
-    r.oct_inv4 = oi * 0x01010101u;
+    r.oct_inv = (sx >= 0.0f ? 1u : 0u) | (sy >= 0.0f ? 2u : 0u) | (sz >= 0.0f ? 4u : 0u);
     return r;
 }
 
 // ---------------------------------------------------------------- node test
-// Returns the 32-bit hit mask: bits 24..31 internal children at priority (slot ^ oct_inv), bits
-// 0..23 triangles (offset from the node's tri_base).
-WPT_HD uint32_t node_hits(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
-                          const RayCtx &r, float tmax)
+// n0 = (p.x, p.y, p.z, e|imask<<24); q[2*axis + side] = the four plane words of that axis/side.
+// Returns the 8-bit mask of children (slot order) whose box the ray segment [tmin, tmax] touches.
+WPT_HD uint32_t node_hits8(const uint4 n0, const uint4 qxl, const uint4 qxh, const uint4 qyl, const uint4 qyh,
+                           const uint4 qzl, const uint4 qzh, const RayCtx &r, float tmax)
 {
     const uint32_t e = n0.w;
-    const float ax = u2f(((e & 0xffu) + 7u) << 23) * r.ix;
-    const float ay = u2f((((e >> 8) & 0xffu) + 7u) << 23) * r.iy;
-    const float az = u2f((((e >> 16) & 0xffu) + 7u) << 23) * r.iz;
-    const float bx = fmaf(-256.0f, ax, (u2f(n0.x) - r.ox) * r.ix);
-    const float by = fmaf(-256.0f, ay, (u2f(n0.y) - r.oy) * r.iy);
-    const float bz = fmaf(-256.0f, az, (u2f(n0.z) - r.oz) * r.iz);
-
-    // near/far plane bytes per axis, by ray direction sign
+    const float ax = u2f((e & 0xffu) << 23) * r.ix;
+    const float ay = u2f(((e >> 8) & 0xffu) << 23) * r.iy;
+    const float az = u2f(((e >> 16) & 0xffu) << 23) * r.iz;
+    const float bx = (u2f(n0.x) - r.ox) * r.ix;
+    const float by = (u2f(n0.y) - r.oy) * r.iy;
+    const float bz = (u2f(n0.z) - r.oz) * r.iz;
     const bool px = r.ix >= 0.0f, py = r.iy >= 0.0f, pz = r.iz >= 0.0f;
-    const uint32_t xn[2] = { px ? n2.x : n3.z, px ? n2.y : n3.w };
-    const uint32_t xf[2] = { px ? n3.z : n2.x, px ? n3.w : n2.y };
-    const uint32_t yn[2] = { py ? n2.z : n4.x, py ? n2.w : n4.y };
-    const uint32_t yf[2] = { py ? n4.x : n2.z, py ? n4.y : n2.w };
-    const uint32_t zn[2] = { pz ? n3.x : n4.z, pz ? n3.y : n4.w };
-    const uint32_t zf[2] = { pz ? n4.z : n3.x, pz ? n4.w : n3.y };
-
-    uint32_t hitmask = 0;
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-        const uint32_t meta4 = h ? n1.w : n1.z;
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = byte_perm(is_inner4 << 3, 0u, 0xba98u);  // 0xff per inner byte
-        const uint32_t bit_index4 = (meta4 ^ (r.oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-#define WPT_CHILD(J)                                                                              \
-        {                                                                                         \
-            const float tx0 = fmaf(q2f<J>(xn[h]), ax, bx), tx1 = fmaf(q2f<J>(xf[h]), ax, bx);     \
-            const float ty0 = fmaf(q2f<J>(yn[h]), ay, by), ty1 = fmaf(q2f<J>(yf[h]), ay, by);     \
-            const float tz0 = fmaf(q2f<J>(zn[h]), az, bz), tz1 = fmaf(q2f<J>(zf[h]), az, bz);     \
-            const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                          \
-            const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                            \
-            if (tn <= tf)                                                                         \
-                hitmask |= ((child_bits4 >> (8 * J)) & 0xffu) << ((bit_index4 >> (8 * J)) & 0xffu); \
-        }
-        WPT_CHILD(0) WPT_CHILD(1) WPT_CHILD(2) WPT_CHILD(3)
-#undef WPT_CHILD
+    float acc = 8388608.0f;   // 2^23: the low mantissa bits collect the hit mask
+#define WPT_PAIR(J, W)                                                                             \
+    {                                                                                              \
+        const uint32_t xn = px ? qxl.W : qxh.W, xf = px ? qxh.W : qxl.W;                           \
+        const uint32_t yn = py ? qyl.W : qyh.W, yf = py ? qyh.W : qyl.W;                           \
+        const uint32_t zn = pz ? qzl.W : qzh.W, zf = pz ? qzh.W : qzl.W;                           \
+        {   /* even child: low halves */                                                           \
+            const float tx0 = fmaf(u2f(xn << 16), ax, bx), tx1 = fmaf(u2f(xf << 16), ax, bx);      \
+            const float ty0 = fmaf(u2f(yn << 16), ay, by), ty1 = fmaf(u2f(yf << 16), ay, by);      \
+            const float tz0 = fmaf(u2f(zn << 16), az, bz), tz1 = fmaf(u2f(zf << 16), az, bz);      \
+            const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                           \
+            const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                             \
+            acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(1 << (2 * J)), acc);                        \
+        }                                                                                          \
+        {   /* odd child: the words as they are */                                                 \
+            const float tx0 = fmaf(u2f(xn), ax, bx), tx1 = fmaf(u2f(xf), ax, bx);        \
+            const float ty0 = fmaf(u2f(yn), ay, by), ty1 = fmaf(u2f(yf), ay, by);        \
+            const float tz0 = fmaf(u2f(zn), az, bz), tz1 = fmaf(u2f(zf), az, bz);        \
+            const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                           \
+            const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                             \
+            acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(2 << (2 * J)), acc);                        \
+        }                                                                                          \
     }
-    return hitmask;
+    WPT_PAIR(0, x) WPT_PAIR(1, y) WPT_PAIR(2, z) WPT_PAIR(3, w)
+#undef WPT_PAIR
+    return f2u(acc) & 0xffu;
 }
 
 // ---------------------------------------------------------------- triangle test
 // t0 = (v0.xyz, e1.x) t1 = (e1.yz, e2.xy) t2 = (e2.z, Ng.xyz).  On accept updates tmax,u,v.
+// Like Embree (triangle_intersector_moeller.h:109-113, rcp = approximation + one Newton step) the
+// accepted hit is scaled by ONE reciprocal of |den| instead of three divisions.
+WPT_HD float rcp_nr(float a)
+{
+#if defined(__CUDA_ARCH__)
+    float r;
+    a = fmaxf(a, 1e-37f);     // accept path only: keeps a denormal |den| from turning into inf
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r * fmaf(-a, r, 2.0f);
+#else
+    return 1.0f / a;
+#endif
+}
 WPT_HD bool tri_hit(const float4 t0, const float4 t1, const float4 t2, const RayCtx &r, float &tmax,
                     float &u, float &v)
 {
@@ -171,9 +176,10 @@ WPT_HD bool tri_hit(const float4 t0, const float4 t1, const float4 t2, const Ray
     if (!(den != 0.0f && U >= 0.0f && V >= 0.0f && U + V <= absden)) return false;
     const float T = u2f(f2u(fmaf(ngx, cx, fmaf(ngy, cy, ngz * cz))) ^ sgn);      // dot(Ng, C)
     if (!(absden * r.tmin < T && T <= absden * tmax)) return false;
-    tmax = T / absden;
-    u = U / absden;
-    v = V / absden;
+    const float rc = rcp_nr(absden);
+    tmax = T * rc;
+    u = U * rc;
+    v = V * rc;
     return true;
 }
 
@@ -191,6 +197,18 @@ WPT_HD uint4 ld_node(const uint4 *p)
     return *p;
 #endif
 }
+// one 256-bit load (sm_100a LDG.E.256): two consecutive 16-byte quads in a single L1 wavefront per
+// lane — divergent traversal is bound by L1 wavefronts per node visit, not by bytes
+WPT_HD void ld_node2(const uint4 *p, uint4 &a, uint4 &b)
+{
+#if defined(__CUDA_ARCH__)
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+        : "l"(p));
+#else
+    a = p[0]; b = p[1];
+#endif
+}
 WPT_HD float4 ld_tri(const float4 *p)
 {
 #if defined(__CUDA_ARCH__)
@@ -200,39 +218,50 @@ WPT_HD float4 ld_tri(const float4 *p)
 #endif
 }
 
-// STACK must provide push(uint2) / pop() / empty()
+// triangle bit mask (bit i = triangle tri_base + i) of the leaf children in `leaf` (slot mask)
+WPT_HD uint32_t leaf_tri_mask(uint32_t leaf, uint32_t meta_lo, uint32_t meta_hi)
+{
+    uint32_t T = 0;
+    while (leaf) {
+        const int s = high_bit(leaf);
+        leaf ^= 1u << s;
+        const uint32_t m = byte_of(meta_lo, meta_hi, (uint32_t)s);
+        T |= (m >> 5) << (m & 31u);     // unary count << offset
+    }
+    return T;
+}
+
+// Traversal entry: x = index of the first internal child of a node, y = (pending internal children,
+// permuted to visiting priority) << 24 | imask.  STACK must provide push(uint2) / pop() / empty().
 template <class STACK>
-WPT_HD Hit trace_ray(const BvhView &bvh, const RayCtx &r, float tmax, STACK &stack)
+WPT_HD Hit trace_ray(const BvhView &bvh, const RayCtx &r, float tmax, STACK &stack, uint64_t *counters = nullptr)
 {
     Hit hit;
     hit.slot = -1; hit.t = tmax; hit.u = 0.0f; hit.v = 0.0f;
-    const uint32_t oct_inv = r.oct_inv4 & 7u;
-    uint2 G; G.x = 0u; G.y = 0x80000000u;  // root: base 0, one pending child, imask 0 -> rel index 0
+    uint2 G; G.x = 0u; G.y = 0x01000000u;  // root: base 0, one pending child, imask 0 -> rel index 0
     for (;;) {
-        uint2 T; T.x = 0u; T.y = 0u;
-        if (G.y & 0xff000000u) {
-            const int bit = high_bit(G.y);
-            G.y &= ~(1u << bit);
-            if (G.y & 0xff000000u) stack.push(G);
-            const uint32_t slot = ((uint32_t)bit - 24u) ^ oct_inv;
-            const uint32_t rel = (uint32_t)pop_count(G.y & ~(0xffffffffu << slot) & 0xffu);
-            const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 5;
-            const uint4 n0 = ld_node(np), n1 = ld_node(np + 1), n2 = ld_node(np + 2), n3 = ld_node(np + 3),
-                        n4 = ld_node(np + 4);
-            const uint32_t hm = node_hits(n0, n1, n2, n3, n4, r, hit.t);
-            G.x = n1.x; G.y = (hm & 0xff000000u) | (n0.w >> 24);
-            T.x = n1.y; T.y = hm & 0x00ffffffu;
-        } else {
-            T = G; G.x = 0u; G.y = 0u;
-        }
-        while (T.y) {
-            const int bit = high_bit(T.y);
-            T.y &= ~(1u << bit);
-            const uint32_t ti = T.x + (uint32_t)bit;
+        const int bit = high_bit(G.y);
+        G.y ^= 1u << bit;
+        if (G.y >> 24) stack.push(G);
+        const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
+        const uint32_t rel = (uint32_t)pop_count(G.y & ((1u << slot) - 1u) & 0xffu);
+        const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 8;
+        uint4 n0, n1, qxl, qxh, qyl, qyh, qzl, qzh;
+        ld_node2(np, n0, n1); ld_node2(np + 2, qxl, qxh); ld_node2(np + 4, qyl, qyh); ld_node2(np + 6, qzl, qzh);
+        const uint32_t h8 = node_hits8(n0, qxl, qxh, qyl, qyh, qzl, qzh, r, hit.t);
+        const uint32_t imask = n0.w >> 24;
+        G.x = n1.x;
+        G.y = (perm8(h8 & imask, r.oct_inv) << 24) | imask;
+        uint32_t T = leaf_tri_mask(h8 & ~imask, n1.z, n1.w);
+        if (counters) { counters[0]++; counters[1] += (uint64_t)pop_count(T); }
+        while (T) {
+            const int tb = high_bit(T);
+            T ^= 1u << tb;
+            const uint32_t ti = n1.y + (uint32_t)tb;
             const float4 *tp = bvh.tris + (size_t)ti * 3;
             if (tri_hit(ld_tri(tp), ld_tri(tp + 1), ld_tri(tp + 2), r, hit.t, hit.u, hit.v)) hit.slot = (int32_t)ti;
         }
-        if (!(G.y & 0xff000000u)) {
+        if (!(G.y >> 24)) {
             if (stack.empty()) break;
             G = stack.pop();
         }
