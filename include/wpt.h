@@ -64,7 +64,7 @@ typedef struct {
 } wpt_bvh_stats;
 
 int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
-/* SAH BVH build on the host, flatten to 80-byte 8-wide quantised nodes + 48-byte triangle blocks,
+/* SAH BVH build on the host, flatten to 64-byte 7-wide quantised nodes + 64-byte triangle blocks (one buffer),
  * one upload to `device`. */
 int  wpt_scene_commit(wpt_scene *s, int device);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);

@@ -39,9 +39,7 @@ struct wpt_scene {
     // device
     int device = -1, num_sms = 0;
     bool committed = false;
-    Node8 *d_nodes = nullptr;
-    Tri48 *d_tris = nullptr;
-    int32_t *d_prim = nullptr;
+    Block64 *d_blocks = nullptr;   // nodes and triangles, bvh.h
     TriAttr48 *d_attr = nullptr;
     float *d_albedo = nullptr;
     uint32_t *d_cursor = nullptr;   // scratch cursor for wpt_intersect
@@ -83,9 +81,9 @@ extern "C" int wpt_scene_create(const wpt_mesh_desc *m, wpt_scene **out)
 static void scene_free_device(wpt_scene *s)
 {
     if (s->device >= 0) cudaSetDevice(s->device);
-    cudaFree(s->d_nodes); cudaFree(s->d_tris); cudaFree(s->d_prim); cudaFree(s->d_attr);
+    cudaFree(s->d_blocks); cudaFree(s->d_attr);
     cudaFree(s->d_albedo); cudaFree(s->d_cursor);
-    s->d_nodes = nullptr; s->d_tris = nullptr; s->d_prim = nullptr; s->d_attr = nullptr;
+    s->d_blocks = nullptr; s->d_attr = nullptr;
     s->d_albedo = nullptr; s->d_cursor = nullptr;
     s->committed = false;
 }
@@ -108,7 +106,7 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
 
     BuiltBvh b;
     const char *err = nullptr;
-    if (!build_bvh8(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
+    if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
         return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
 
     // per-ORIGINAL-triangle shading attributes: 3 vertex normals + material, one 48 B gather per hit
@@ -145,34 +143,29 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     WPT_CUDA(cudaGetDeviceProperties(&prop, device));
     s->device = device;
     s->num_sms = prop.multiProcessorCount;
-    WPT_CUDA(cudaMalloc(&s->d_nodes, b.nodes.size() * sizeof(Node8)));
-    WPT_CUDA(cudaMalloc(&s->d_tris, b.tris.size() * sizeof(Tri48)));
-    WPT_CUDA(cudaMalloc(&s->d_prim, b.prim_id.size() * sizeof(int32_t)));
+    WPT_CUDA(cudaMalloc(&s->d_blocks, b.blocks.size() * sizeof(Block64)));
     WPT_CUDA(cudaMalloc(&s->d_attr, attr.size() * sizeof(TriAttr48)));
     WPT_CUDA(cudaMalloc(&s->d_albedo, s->albedo.size() * sizeof(float)));
     WPT_CUDA(cudaMalloc(&s->d_cursor, 64 * sizeof(uint32_t)));
-    WPT_CUDA(cudaMemcpy(s->d_nodes, b.nodes.data(), b.nodes.size() * sizeof(Node8), cudaMemcpyHostToDevice));
-    WPT_CUDA(cudaMemcpy(s->d_tris, b.tris.data(), b.tris.size() * sizeof(Tri48), cudaMemcpyHostToDevice));
-    WPT_CUDA(cudaMemcpy(s->d_prim, b.prim_id.data(), b.prim_id.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaDeviceSynchronize());
     const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 
-    s->view.nodes = reinterpret_cast<const uint4 *>(s->d_nodes);
-    s->view.tris = reinterpret_cast<const float4 *>(s->d_tris);
-    s->view.prim_id = s->d_prim;
-    s->view.n_nodes = (uint32_t)b.nodes.size();
-    s->view.n_tris = (uint32_t)b.tris.size();
+    s->view.blocks = reinterpret_cast<const uint4 *>(s->d_blocks);
+    s->view.n_blocks = (uint32_t)b.blocks.size();
+    s->view.n_nodes = b.n_nodes;
+    s->view.n_tris = b.n_tris;
     s->stats.n_triangles = s->n_tris;
-    s->stats.n_nodes = (uint32_t)b.nodes.size();
-    s->stats.n_leaf_slots = (uint32_t)b.tris.size();
+    s->stats.n_nodes = b.n_nodes;
+    s->stats.n_leaf_slots = b.n_tris;
     s->stats.max_depth = b.max_depth;
     s->stats.sah_cost = b.sah_cost;
     s->stats.build_ms = b.build_ms;
     s->stats.upload_ms = up_ms;
-    s->stats.node_bytes = b.nodes.size() * sizeof(Node8);
-    s->stats.tri_bytes = b.tris.size() * sizeof(Tri48) + b.prim_id.size() * sizeof(int32_t);
+    s->stats.node_bytes = (uint64_t)b.n_nodes * sizeof(Block64);
+    s->stats.tri_bytes = (uint64_t)b.n_tris * sizeof(Block64);
     s->stats.attr_bytes = attr.size() * sizeof(TriAttr48);
     s->committed = true;
     return WPT_OK;

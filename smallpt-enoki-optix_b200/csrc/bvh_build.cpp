@@ -157,27 +157,25 @@ inline void cross_fma(const float a[3], const float b[3], float o[3])
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
-// Collapse: SAH-optimal BVH2 -> BVH8 by dynamic programming over "cost of representing the
-// subtree of n with at most i roots" (Ylitie et al. 2017, §4.1).
-//   C(n,1)   = min( A_n*c_p*P_n  [P_n <= 3],  A_n*c_n + Cd(n,8) )
+// Collapse: SAH-optimal BVH2 -> BVH7 by dynamic programming over "cost of representing the
+// subtree of n with at most i roots" (Ylitie et al. 2017, §4.1), W = kWidth:
+//   C(n,1)   = min( A_n*c_p*P_n  [P_n <= 3],  A_n*c_n + Cd(n,W) )
 //   C(n,i>1) = min( Cd(n,i), C(n,i-1) )
 //   Cd(n,j)  = min_{0<k<j} C(left,k) + C(right,j-k)
 namespace {
 
+constexpr int W = kWidth;
+
 struct Dp {
-    float   c[7];      // C(n,i), i = 1..7 at c[i-1]
-    uint8_t k[7];      // for i>=2: split k of Cd(n,i) if chosen, 0 = "same as i-1"
-    uint8_t k8;        // split of Cd(n,8)
+    float   c[W - 1];  // C(n,i), i = 1..W-1 at c[i-1]
+    uint8_t k[W - 1];  // for i>=2: split k of Cd(n,i) if chosen, 0 = "same as i-1"
+    uint8_t kw;        // split of Cd(n,W)
     uint8_t leaf;      // C(n,1) picked the leaf
 };
 
 struct Collapser {
     const Node2 *n2;
     const Dp *dp;
-    const uint32_t *idx;
-    const float *pos;
-    const int32_t *trip;
-    BuiltBvh *out;
 
     // children of the wide node rooted at BVH2 node r
     int gather_root(uint32_t r, uint32_t *kids) const
@@ -185,9 +183,9 @@ struct Collapser {
         int n = 0;
         const Node2 &nd = n2[r];
         if (nd.count == 1) { kids[n++] = r; return n; }
-        const int k = dp[r].k8;
+        const int k = dp[r].kw;
         gather(r + 1, k, kids, n);
-        gather(nd.right, 8 - k, kids, n);
+        gather(nd.right, W - k, kids, n);
         return n;
     }
     void gather(uint32_t v, int i, uint32_t *kids, int &n) const
@@ -203,77 +201,56 @@ struct Collapser {
     bool is_leaf(uint32_t v) const { return n2[v].count == 1 || dp[v].leaf; }
 };
 
-inline uint8_t exp_for_extent(float extent, float maxabs)
+// biased exponent e of the quantisation step 2^(e-127): the smallest power of two s with 240*s >=
+// extent (head-room for the margins below) and s >= 2^-17 * maxabs, so that even a flat node keeps a
+// margin (s/8 ~ 2^-20 * |coordinate|) that dominates the float rounding of (p - o) / d in the
+// device's slab test.
+inline int exp_for_extent(float extent, float maxabs)
 {
-    // smallest power of two s with 253*s >= extent (2 steps of head-room for the margins below) and
-    // s >= 2^-17 * maxabs, so that even a flat node keeps a margin (s/32 ~ 2^-22 * |coordinate|) that
-    // dominates the float rounding of (p - o) / d in the device's slab test.
-    const double need = std::max((double)extent / 253.0, std::ldexp((double)maxabs, -17));
-    if (!(need > 0.0)) return (uint8_t)(127 - 100);
+    const double need = std::max((double)extent / 240.0, std::ldexp((double)maxabs, -17));
+    if (!(need > 0.0)) return 127 - 100;
     int e;
     const double m = std::frexp(need, &e);  // need = m * 2^e, m in [0.5,1)
     int ex = (m == 0.5) ? e - 1 : e;
     ex = std::max(-100, std::min(100, ex));
-    return (uint8_t)(ex + 127);
+    return ex + 127;
 }
+
+inline double node_scale(const Node7 &n, int k)
+{
+    const uint8_t eb = k == 0 ? n.xlo[7] : k == 1 ? n.xhi[7] : n.ylo[7];   // stored as e + 8
+    return std::ldexp(1.0, (int)eb - 8 - 127);
+}
+inline const uint8_t *plane_lo(const Node7 &n, int k) { return k == 0 ? n.xlo : k == 1 ? n.ylo : n.zlo; }
+inline const uint8_t *plane_hi(const Node7 &n, int k) { return k == 0 ? n.xhi : k == 1 ? n.yhi : n.zhi; }
 
 }  // namespace
 
-// ---- bfloat16 plane encoding (see bvh.h / trace_core.h) -------------------------------------------
-namespace {
-inline float bits_to_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
-inline uint32_t float_to_bits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
-// largest bfloat16 <= x, x >= 0
-inline uint16_t bf16_floor_pos(double x)
+uint32_t node_imask(const Node7 &n) { return n.yhi[7]; }
+uint32_t node_tri_count(const Node7 &n, int slot)
 {
-    if (!(x > 0.0)) return 0;
-    float f = (float)x;
-    if ((double)f > x) f = std::nextafterf(f, -kInf);
-    return (uint16_t)(float_to_bits(f) >> 16);   // truncation = floor for positive values
+    const uint32_t c = (uint32_t)n.zlo[7] | ((uint32_t)n.zhi[7] << 8);
+    return (c >> (2 * slot)) & 3u;
 }
-// what the device sees for a plane stored in the HIGH half of a word whose low half is `low`
-inline double decode_high(uint16_t stored, uint16_t low) { return (double)bits_to_float(((uint32_t)stored << 16) | low); }
-inline double decode_low(uint16_t stored) { return (double)bits_to_float((uint32_t)stored << 16); }
+bool node_slot_empty(const Node7 &n, int slot)
+{
+    return !((node_imask(n) >> slot) & 1u) && node_tri_count(n, slot) == 0;
+}
 
-// lower plane: the largest encodable value whose DECODED value is <= x
-inline uint16_t enc_lo(double x, bool high_half, uint16_t low)
+// world-space box the traversal kernel tests for child `slot` (before float rounding of the slab test)
+void node_child_bounds(const Node7 &n, int slot, float lo[3], float hi[3])
 {
-    uint16_t s = bf16_floor_pos(x);
-    if (!high_half) return s;
-    while (s > 0 && decode_high(s, low) > x) s--;
-    if (s == 0 && decode_high(0, low) > x) return 0x8000u;   // -0 | garbage = a tiny negative number
-    return s;
-}
-// upper plane: the smallest encodable value whose decoded value is >= x
-inline uint16_t enc_hi(double x, bool high_half, uint16_t low)
-{
-    uint16_t s = bf16_floor_pos(x);
-    while ((high_half ? decode_high(s, low) : decode_low(s)) < x) s++;
-    return s;
-}
-constexpr uint16_t kEmptyLo = 0x4680u;  // +16384: an inverted box, never hit
-constexpr uint16_t kEmptyHi = 0xC680u;  // -16384
-}  // namespace
-
-// conservative world-space box the traversal kernel effectively tests for child `slot`
-void node_child_bounds(const Node8 &n, int slot, float lo[3], float hi[3])
-{
-    const int j = slot >> 1;
-    const bool high = slot & 1;
     for (int k = 0; k < 3; k++) {
-        const double s = std::ldexp(1.0, (int)n.e[k] - 127);
-        const uint32_t wl = n.planes[k][0][j], wh = n.planes[k][1][j];
-        const double ql = high ? (double)bits_to_float(wl) : decode_low((uint16_t)(wl & 0xffffu));
-        const double qh = high ? (double)bits_to_float(wh) : decode_low((uint16_t)(wh & 0xffffu));
-        lo[k] = (float)((double)n.p[k] + s * ql);
-        hi[k] = (float)((double)n.p[k] + s * qh);
-        // the float conversions above round to nearest: push outwards so the check stays strict
-        if ((double)lo[k] < (double)n.p[k] + s * ql) lo[k] = std::nextafterf(lo[k], kInf);
-        if ((double)hi[k] > (double)n.p[k] + s * qh) hi[k] = std::nextafterf(hi[k], -kInf);
+        const double s = node_scale(n, k);
+        const double l = (double)n.p[k] + s * plane_lo(n, k)[slot], h = (double)n.p[k] + s * plane_hi(n, k)[slot];
+        lo[k] = (float)l; hi[k] = (float)h;
+        // the float conversions round to nearest: push inwards so the containment check stays strict
+        if ((double)lo[k] < l) lo[k] = std::nextafterf(lo[k], kInf);
+        if ((double)hi[k] > h) hi[k] = std::nextafterf(hi[k], -kInf);
     }
 }
 
-bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
+bool build_bvh7(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
                 BuiltBvh &out, const char **err, int threads)
 {
     static const char *e_empty = "scene has no triangles";
@@ -320,19 +297,19 @@ bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets,
         Dp &d = dp[v];
         const float A = nd.b.half_area() / root_area;
         if (nd.count == 1) {
-            for (int i = 0; i < 7; i++) { d.c[i] = A * kCostTri; d.k[i] = 0; }
-            d.k8 = 0;
+            for (int i = 0; i < W - 1; i++) { d.c[i] = A * kCostTri; d.k[i] = 0; }
+            d.kw = 0;
             d.leaf = 1;
             continue;
         }
         const Dp &L = dp[v + 1], &R = dp[nd.right];
-        float cd[9];
-        uint8_t kd[9];
-        for (int j = 2; j <= 8; j++) {
+        float cd[W + 1];
+        uint8_t kd[W + 1];
+        for (int j = 2; j <= W; j++) {
             float best = kInf;
             uint8_t bk = 1;
             for (int k = 1; k < j; k++) {
-                if (k > 7 || j - k > 7) continue;
+                if (k > W - 1 || j - k > W - 1) continue;
                 const float c = L.c[k - 1] + R.c[j - k - 1];
                 if (c < best) { best = c; bk = (uint8_t)k; }
             }
@@ -340,133 +317,128 @@ bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets,
             kd[j] = bk;
         }
         const float c_leaf = nd.count <= (uint32_t)kMaxLeafTris ? A * kCostTri * (float)nd.count : kInf;
-        const float c_int = A * kCostNode + cd[8];
-        d.k8 = kd[8];
+        const float c_int = A * kCostNode + cd[W];
+        d.kw = kd[W];
         d.leaf = c_leaf <= c_int;
         d.c[0] = d.leaf ? c_leaf : c_int;
         d.k[0] = 0;
-        for (int i = 2; i <= 7; i++) {
+        for (int i = 2; i <= W - 1; i++) {
             if (cd[i] < d.c[i - 2]) { d.c[i - 1] = cd[i]; d.k[i - 1] = kd[i]; }
             else { d.c[i - 1] = d.c[i - 2]; d.k[i - 1] = 0; }
         }
     }
 
-    // ---- emit, breadth first so siblings are contiguous
-    Collapser col{n2.data(), dp.data(), idx.data(), positions, triplets, &out};
-    struct Work { uint32_t bvh2, depth; };
+    // ---- emit, breadth first: the children of a node (internal nodes, then leaf triangles) are one
+    // contiguous run of blocks
+    Collapser col{n2.data(), dp.data()};
+    struct Work { uint32_t bvh2, block, depth; };
     std::vector<Work> queue;
     queue.reserve(n_tris / 2 + 16);
-    out.nodes.reserve(n_tris / 2 + 16);
-    out.tris.reserve(n_tris);
-    out.prim_id.reserve(n_tris);
-    out.nodes.emplace_back();
-    queue.push_back({0u, 1u});
+    out.blocks.reserve((size_t)n_tris + n_tris / 3 + 16);
+    out.blocks.emplace_back();
+    queue.push_back({0u, 0u, 1u});
     double sah = 0.0;
     for (size_t qi = 0; qi < queue.size(); qi++) {
         const Work w = queue[qi];
         out.max_depth = std::max(out.max_depth, w.depth);
-        uint32_t kids[8];
+        out.n_nodes++;
+        uint32_t kids[W];
         const int nk = col.gather_root(w.bvh2, kids);
         const Box nb = n2[w.bvh2].b;
         sah += (double)(nb.half_area() / root_area) * kCostNode;
 
         // slot assignment: slot s should hold the child lying furthest towards corner s
         // (bit k of s set = +axis k), so that traversal priority is slot XOR ray octant.
-        int slot_of[8];
+        int slot_of[W];
         {
-            float cost[8][8];
+            float cost[W][W];
             float nc[3];
             for (int k = 0; k < 3; k++) nc[k] = 0.5f * (nb.lo[k] + nb.hi[k]);
             for (int c = 0; c < nk; c++) {
                 const Box &cb = n2[kids[c]].b;
                 float dc[3];
                 for (int k = 0; k < 3; k++) dc[k] = 0.5f * (cb.lo[k] + cb.hi[k]) - nc[k];
-                for (int s = 0; s < 8; s++)
+                for (int s = 0; s < W; s++)
                     cost[c][s] = ((s & 1) ? dc[0] : -dc[0]) + ((s & 2) ? dc[1] : -dc[1]) + ((s & 4) ? dc[2] : -dc[2]);
             }
-            bool cu[8] = {false}, su[8] = {false};
+            bool cu[W] = {false}, su[W] = {false};
             for (int it = 0; it < nk; it++) {
                 float best = -kInf;
                 int bc = -1, bs = -1;
                 for (int c = 0; c < nk; c++) {
                     if (cu[c]) continue;
-                    for (int s = 0; s < 8; s++)
+                    for (int s = 0; s < W; s++)
                         if (!su[s] && cost[c][s] > best) { best = cost[c][s]; bc = c; bs = s; }
                 }
                 cu[bc] = true; su[bs] = true; slot_of[bc] = bs;
             }
         }
-        int child_in_slot[8];
-        for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+        int child_in_slot[W];
+        for (int s = 0; s < W; s++) child_in_slot[s] = -1;
         for (int c = 0; c < nk; c++) child_in_slot[slot_of[c]] = c;
 
-        Node8 node;
+        Node7 node;
         std::memset(&node, 0, sizeof node);
+        int eb[3];
         for (int k = 0; k < 3; k++) {
             const float maxabs = std::max(std::fabs(nb.lo[k]), std::fabs(nb.hi[k]));
-            node.e[k] = exp_for_extent(nb.hi[k] - nb.lo[k], maxabs);
-            // origin sits s/32 below the true lower corner: every quantised plane keeps a margin
-            const double sc = std::ldexp(1.0, (int)node.e[k] - 127);
-            float p = (float)((double)nb.lo[k] - sc / 32.0);
-            while ((double)p > (double)nb.lo[k] - sc / 64.0) p = std::nextafterf(p, -kInf);
+            eb[k] = exp_for_extent(nb.hi[k] - nb.lo[k], maxabs);
+            // origin sits s/4 below the true lower corner: every quantised plane keeps a margin
+            const double sc = std::ldexp(1.0, eb[k] - 127);
+            float p = (float)((double)nb.lo[k] - sc / 4.0);
+            while ((double)p > (double)nb.lo[k] - sc / 8.0) p = std::nextafterf(p, -kInf);
             node.p[k] = p;
         }
-        node.child_base = (uint32_t)out.nodes.size();
-        node.tri_base = (uint32_t)out.tris.size();
-        uint32_t tri_off = 0;
-        uint16_t qlo[3][8], qhi[3][8];
-        for (int s = 0; s < 8; s++)
-            for (int k = 0; k < 3; k++) { qlo[k][s] = kEmptyLo; qhi[k][s] = kEmptyHi; }
-        // even slots first: the odd child of a pair is rounded against the bits its sibling leaves
-        // in the low half of the shared word
-        for (int pass = 0; pass < 2; pass++) {
-            for (int s = pass; s < 8; s += 2) {
-                const int c = child_in_slot[s];
-                if (c < 0) continue;
-                const Node2 &cn = n2[kids[c]];
-                for (int k = 0; k < 3; k++) {
-                    const double sc = std::ldexp(1.0, (int)node.e[k] - 127);
-                    const double xl = ((double)cn.b.lo[k] - (double)node.p[k]) / sc - 1.0 / 64.0;
-                    const double xh = ((double)cn.b.hi[k] - (double)node.p[k]) / sc + 1.0 / 64.0;
-                    qlo[k][s] = enc_lo(xl, pass == 1, qlo[k][s & ~1]);
-                    qhi[k][s] = enc_hi(xh, pass == 1, qhi[k][s & ~1]);
-                }
+        uint8_t *plo[3] = {node.xlo, node.ylo, node.zlo}, *phi[3] = {node.xhi, node.yhi, node.zhi};
+        uint32_t imask = 0, cnt2 = 0, n_int = 0, n_leaf_tris = 0;
+        for (int s = 0; s < W; s++) {
+            const int c = child_in_slot[s];
+            if (c < 0) {
+                for (int k = 0; k < 3; k++) { plo[k][s] = 255; phi[k][s] = 0; }   // inverted: never hit
+                continue;
             }
+            const Node2 &cn = n2[kids[c]];
+            for (int k = 0; k < 3; k++) {
+                const double sc = std::ldexp(1.0, eb[k] - 127);
+                const double ql = std::floor(((double)cn.b.lo[k] - (double)node.p[k]) / sc - 1.0 / 8.0);
+                const double qh = std::ceil(((double)cn.b.hi[k] - (double)node.p[k]) / sc + 1.0 / 8.0);
+                plo[k][s] = (uint8_t)std::max(0.0, std::min(255.0, ql));
+                phi[k][s] = (uint8_t)std::max(0.0, std::min(255.0, qh));
+            }
+            if (col.is_leaf(kids[c])) { cnt2 |= cn.count << (2 * s); n_leaf_tris += cn.count; }
+            else { imask |= 1u << s; n_int++; }
         }
-        for (int k = 0; k < 3; k++)
-            for (int j = 0; j < 4; j++) {
-                node.planes[k][0][j] = (uint32_t)qlo[k][2 * j] | ((uint32_t)qlo[k][2 * j + 1] << 16);
-                node.planes[k][1][j] = (uint32_t)qhi[k][2 * j] | ((uint32_t)qhi[k][2 * j + 1] << 16);
-            }
-        for (int s = 0; s < 8; s++) {
+        node.xlo[7] = (uint8_t)(eb[0] + 8); node.xhi[7] = (uint8_t)(eb[1] + 8); node.ylo[7] = (uint8_t)(eb[2] + 8);
+        node.yhi[7] = (uint8_t)imask;
+        node.zlo[7] = (uint8_t)(cnt2 & 0xffu); node.zhi[7] = (uint8_t)(cnt2 >> 8);
+        node.base = (uint32_t)out.blocks.size();
+        out.blocks.resize(out.blocks.size() + n_int + n_leaf_tris);
+        uint32_t next_node = node.base, next_tri = node.base + n_int;
+        for (int s = 0; s < W; s++) {
             const int c = child_in_slot[s];
             if (c < 0) continue;
             const uint32_t v = kids[c];
             const Node2 &cn = n2[v];
             if (col.is_leaf(v)) {
-                const uint32_t cnt = cn.count;
-                node.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | tri_off);
-                for (uint32_t i = cn.first; i < cn.first + cnt; i++) {
+                for (uint32_t i = cn.first; i < cn.first + cn.count; i++) {
                     const uint32_t prim = idx[i];
                     const float *a = positions + 3 * (size_t)triplets[3 * prim + 0];
                     const float *b = positions + 3 * (size_t)triplets[3 * prim + 1];
                     const float *c3 = positions + 3 * (size_t)triplets[3 * prim + 2];
-                    Tri48 t;
+                    Tri64 t;
+                    std::memset(&t, 0, sizeof t);
                     for (int k = 0; k < 3; k++) { t.v0[k] = a[k]; t.e1[k] = a[k] - b[k]; t.e2[k] = c3[k] - a[k]; }
                     cross_fma(t.e2, t.e1, t.ng);
-                    out.tris.push_back(t);
-                    out.prim_id.push_back((int32_t)prim);
+                    t.prim = (int32_t)prim;
+                    out.blocks[next_tri++].tri = t;
+                    out.n_tris++;
                 }
-                tri_off += cnt;
-                sah += (double)(cn.b.half_area() / root_area) * kCostTri * cnt;
+                sah += (double)(cn.b.half_area() / root_area) * kCostTri * cn.count;
             } else {
-                node.meta[s] = 0xffu;
-                node.imask |= (uint8_t)(1u << s);
-                out.nodes.emplace_back();
-                queue.push_back({v, w.depth + 1});
+                queue.push_back({v, next_node++, w.depth + 1});
             }
         }
-        out.nodes[qi] = node;
+        out.blocks[w.block].node = node;
     }
     out.sah_cost = sah;
     if (out.max_depth > (uint32_t)kStackSize - 1) { *err = e_depth; return false; }

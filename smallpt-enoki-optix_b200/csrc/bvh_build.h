@@ -8,9 +8,8 @@
 namespace wpt {
 
 struct BuiltBvh {
-    std::vector<Node8>   nodes;    // nodes[0] is the root
-    std::vector<Tri48>   tris;     // leaf order
-    std::vector<int32_t> prim_id;  // leaf slot -> original face index
+    std::vector<Block64> blocks;   // blocks[0] is the root node
+    uint32_t n_nodes = 0, n_tris = 0;
     uint32_t max_depth = 0;        // wide-tree depth (root = 1)
     double   sah_cost = 0.0;
     double   build_ms = 0.0;
@@ -18,11 +17,14 @@ struct BuiltBvh {
 
 // positions f32[3*n_pos], triplets i32[3*n_tris].  Returns false + message on invalid input
 // (index out of range, non-finite vertex, depth limit).
-bool build_bvh8(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
+bool build_bvh7(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
                 BuiltBvh &out, const char **err, int threads = 0);
 
-// Decode helpers shared with the tests: child box of slot i in world space (conservative bounds the
-// traversal kernel effectively tests).
-void node_child_bounds(const Node8 &n, int slot, float lo[3], float hi[3]);
+// Decode helpers shared with the tests
+uint32_t node_imask(const Node7 &n);
+uint32_t node_tri_count(const Node7 &n, int slot);
+bool     node_slot_empty(const Node7 &n, int slot);
+// child box of slot i in world space (the bounds the traversal kernel effectively tests)
+void node_child_bounds(const Node7 &n, int slot, float lo[3], float hi[3]);
 
 }  // namespace wpt

@@ -16,47 +16,57 @@ int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uin
 {
     BuiltBvh b;
     const char *err = nullptr;
-    if (!build_bvh8(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
+    if (!build_bvh7(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
     // structural validation: every triangle appears exactly once; every child's quantised box
-    // contains the geometry below it; internal children are contiguous.
-    std::vector<int> seen(n_tris, 0);
+    // contains the geometry below it; every block is referenced exactly once.
+    std::vector<int> seen(n_tris, 0), block_refs(b.blocks.size(), 0);
     long problems = 0;
-    struct Item { uint32_t node; };
-    std::vector<uint32_t> stack{0u};
-    std::vector<float> lo_of(b.nodes.size() * 3), hi_of(b.nodes.size() * 3);
-    // bottom-up true bounds via recursion (explicit post-order)
-    std::vector<std::pair<uint32_t, int>> st{{0u, 0}};
-    std::vector<uint32_t> order;
+    std::vector<float> lo_of(b.blocks.size() * 3), hi_of(b.blocks.size() * 3);
+    std::vector<uint32_t> st{0u}, order;
+    block_refs[0] = 1;
     while (!st.empty()) {
-        auto [n, _] = st.back(); st.pop_back();
+        const uint32_t n = st.back(); st.pop_back();
         order.push_back(n);
-        const Node8 &nd = b.nodes[n];
+        const Node7 &nd = b.blocks[n].node;
         int rel = 0;
-        for (int s = 0; s < 8; s++) if (nd.imask & (1 << s)) st.push_back({nd.child_base + rel++, 0});
+        for (int s = 0; s < kWidth; s++)
+            if (node_imask(nd) & (1u << s)) {
+                const uint32_t c = nd.base + rel++;
+                if (c >= b.blocks.size()) { problems++; continue; }
+                block_refs[c]++;
+                st.push_back(c);
+            }
     }
     for (size_t oi = order.size(); oi-- > 0;) {
         const uint32_t n = order[oi];
-        const Node8 &nd = b.nodes[n];
+        const Node7 &nd = b.blocks[n].node;
         float nlo[3] = {INFINITY, INFINITY, INFINITY}, nhi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        int rel = 0;
-        for (int s = 0; s < 8; s++) {
-            if (!nd.meta[s]) continue;
+        const uint32_t n_int = (uint32_t)pop_count(node_imask(nd));
+        uint32_t rel = 0, tri_off = 0;
+        for (int s = 0; s < kWidth; s++) {
+            if (node_slot_empty(nd, s)) continue;
             float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
-            if (nd.imask & (1 << s)) {
-                const uint32_t c = nd.child_base + rel++;
+            if (node_imask(nd) & (1u << s)) {
+                const uint32_t c = nd.base + rel++;
                 for (int k = 0; k < 3; k++) { clo[k] = lo_of[3 * c + k]; chi[k] = hi_of[3 * c + k]; }
             } else {
-                const int cnt = pop_count(nd.meta[s] >> 5), off = nd.meta[s] & 31;
-                for (int i = 0; i < cnt; i++) {
-                    const uint32_t slot = nd.tri_base + off + i;
-                    const int32_t prim = b.prim_id[slot];
+                const uint32_t cnt = node_tri_count(nd, s);
+                for (uint32_t i = 0; i < cnt; i++) {
+                    const uint32_t blk = nd.base + n_int + tri_off + i;
+                    if (blk >= b.blocks.size()) { problems++; continue; }
+                    block_refs[blk]++;
+                    const Tri64 &t = b.blocks[blk].tri;
+                    const int32_t prim = t.prim;
                     if (prim < 0 || (uint32_t)prim >= n_tris) { problems++; continue; }
                     seen[prim]++;
                     for (int v = 0; v < 3; v++) {
                         const float *p = pos + 3 * (size_t)idx[3 * prim + v];
                         for (int k = 0; k < 3; k++) { clo[k] = fminf(clo[k], p[k]); chi[k] = fmaxf(chi[k], p[k]); }
                     }
+                    const float *p0 = pos + 3 * (size_t)idx[3 * prim];
+                    for (int k = 0; k < 3; k++) if (t.v0[k] != p0[k]) problems++;
                 }
+                tri_off += cnt;
             }
             float qlo[3], qhi[3];
             node_child_bounds(nd, s, qlo, qhi);
@@ -68,7 +78,9 @@ int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uin
         for (int k = 0; k < 3; k++) { lo_of[3 * n + k] = nlo[k]; hi_of[3 * n + k] = nhi[k]; }
     }
     for (uint32_t i = 0; i < n_tris; i++) if (seen[i] != 1) problems++;
-    stats[0] = (double)b.nodes.size(); stats[1] = (double)b.tris.size(); stats[2] = b.max_depth;
+    for (int r : block_refs) if (r != 1) problems++;
+    if (order.size() != b.n_nodes || b.n_tris != n_tris) problems++;
+    stats[0] = (double)b.n_nodes; stats[1] = (double)b.n_tris; stats[2] = b.max_depth;
     stats[3] = b.sah_cost; stats[4] = b.build_ms; stats[5] = (double)problems;
     return 0;
 }
@@ -81,13 +93,12 @@ int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *id
 {
     BuiltBvh b;
     const char *err = nullptr;
-    if (!build_bvh8(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
+    if (!build_bvh7(pos, n_pos, idx, n_tris, b, &err)) { fprintf(stderr, "build failed: %s\n", err); return 1; }
     BvhView view;
-    view.nodes = reinterpret_cast<const uint4 *>(b.nodes.data());
-    view.tris = reinterpret_cast<const float4 *>(b.tris.data());
-    view.prim_id = b.prim_id.data();
-    view.n_nodes = (uint32_t)b.nodes.size();
-    view.n_tris = (uint32_t)b.tris.size();
+    view.blocks = reinterpret_cast<const uint4 *>(b.blocks.data());
+    view.n_blocks = (uint32_t)b.blocks.size();
+    view.n_nodes = b.n_nodes;
+    view.n_tris = b.n_tris;
     uint64_t nodes_visited = 0, tris_tested = 0;
 #pragma omp parallel for schedule(dynamic, 1024) reduction(+ : nodes_visited, tris_tested)
     for (int64_t i = 0; i < (int64_t)n; i++) {
@@ -96,8 +107,8 @@ int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *id
         uint64_t c[2] = {0, 0};
         const Hit h = trace_ray(view, r, tmax, st, c);
         nodes_visited += c[0]; tris_tested += c[1];
-        id[i] = h.slot < 0 ? -1 : view.prim_id[h.slot];
-        if (h.slot >= 0) { t[i] = h.t; u[i] = h.u; v[i] = h.v; }
+        id[i] = h.prim;
+        if (h.prim >= 0) { t[i] = h.t; u[i] = h.u; v[i] = h.v; }
     }
     if (counters) { counters[0] = (double)nodes_visited; counters[1] = (double)tris_tested; }
     return 0;

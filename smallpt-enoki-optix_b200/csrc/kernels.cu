@@ -69,8 +69,8 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
                  uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
 {
     __shared__ uint2 sstack[kSmemStack * kTraceBlock];
-    __shared__ uint8_t perm_lut[8 * 256];   // perm_lut[o*256 + m] = perm8(m, o): visiting priority of slot mask m
-    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += kTraceBlock) perm_lut[i] = (uint8_t)perm8(i & 255u, i >> 8);
+    __shared__ uint8_t perm_lut[8 * 128];   // perm_lut[o*128 + m] = perm8(m, o): visiting priority of slot mask m
+    for (uint32_t i = threadIdx.x; i < 8u * 128u; i += kTraceBlock) perm_lut[i] = (uint8_t)perm8(i & 127u, i >> 7);
     __syncthreads();
     const uint32_t n = n_ptr ? *n_ptr : n_static;
     if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
@@ -86,7 +86,7 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
     Hit hit;
     uint2 G;
     G.x = G.y = 0u;
-    hit.slot = -1; hit.t = hit.u = hit.v = 0.0f;
+    hit.prim = -1; hit.t = hit.u = hit.v = 0.0f;
 
     for (;;) {
         // ---- refill idle lanes once too few of the warp are working: one warp-aggregated atomic on
@@ -106,8 +106,8 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
                     float ox, oy, oz, dx, dy, dz, t0, t1;
                     if (i < n && io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) {
                         r = make_ray(ox, oy, oz, dx, dy, dz, t0);
-                        lut = perm_lut + r.oct_inv * 256u;
-                        hit.slot = -1; hit.t = t1; hit.u = hit.v = 0.0f;
+                        lut = perm_lut + r.oct_inv * 128u;
+                        hit.prim = -1; hit.t = t1; hit.u = hit.v = 0.0f;
                         G.x = 0u; G.y = 0x01000000u;
                         sp = 0;
                         ray_i = i;
@@ -132,26 +132,26 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
             }
             const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
             const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
-            const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 8;
-            uint4 n0, n1, qxl, qxh, qyl, qyh, qzl, qzh;
-            ld_node2(np, n0, n1); ld_node2(np + 2, qxl, qxh); ld_node2(np + 4, qyl, qyh); ld_node2(np + 6, qzl, qzh);
-            const uint32_t h8 = node_hits8(n0, qxl, qxh, qyl, qyh, qzl, qzh, r, hit.t);
-            const uint32_t imask = n0.w >> 24;
-            G.x = n1.x;
-            G.y = ((uint32_t)lut[h8 & imask] << 24) | imask;
-            uint32_t T = leaf_tri_mask(h8 & ~imask, n1.z, n1.w);
+            const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
+            uint4 q0, q1, q2, q3;
+            ld_block_half(np, q0, q1); ld_block_half(np + 2, q2, q3);
+            const uint32_t h7 = node_hits7(q0, q1, q2, q3, r, hit.t);
+            const uint32_t imask = q2.w >> 24;
+            G.x = q0.w;
+            G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
+            uint32_t T = leaf_tri_mask(h7 & ~imask, (q3.y >> 24) | ((q3.w >> 24) << 8));
+            const uint32_t tri0 = q0.w + (uint32_t)__popc(imask);
             while (T) {
                 const int tb = 31 - __clz((int)T);
                 T ^= 1u << tb;
-                const uint32_t ti = n1.y + (uint32_t)tb;
-                const float4 *tp = bvh.tris + (size_t)ti * 3;
-                const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-                if (tri_hit(t0, t1, t2, r, hit.t, hit.u, hit.v)) hit.slot = (int32_t)ti;
+                const uint4 *tp = bvh.blocks + (size_t)(tri0 + (uint32_t)tb) * 4;
+                uint4 ta, tb4, tc, td;
+                ld_block_half(tp, ta, tb4); ld_block_half(tp + 2, tc, td);
+                if (tri_hit(as_f4(ta), as_f4(tb4), as_f4(tc), r, hit.t, hit.u, hit.v)) hit.prim = (int32_t)td.x;
             }
             if (!(G.y >> 24)) {
                 if (sp == 0) {
-                    const int32_t prim = hit.slot < 0 ? -1 : __ldg(bvh.prim_id + hit.slot);
-                    io.store(ray_i, prim, hit.t, hit.u, hit.v);
+                    io.store(ray_i, hit.prim, hit.t, hit.u, hit.v);
                     active = false;
                 } else {
                     sp--;
@@ -159,6 +159,169 @@ trace_persistent(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_
                 }
             }
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// persistent traversal with a WARP-SHARED TRIANGLE QUEUE (the default trace kernel)
+// ------------------------------------------------------------------------------------------------
+// ncu of the per-lane loop above (profiles/): on incoherent rays the triangle loop ran with 2.8 of
+// 32 lanes and took 40 % of all issued instructions.  Here a node step only APPENDS the triangles
+// of the leaves it hit to a queue shared by the warp; whenever 32 are queued, every lane tests one
+// of them — for whichever ray of the warp it belongs to — and folds the result into that ray's
+// closest hit with a shared-memory atomicMin on the (positive) float bits of t.  Ray records and
+// closest hits therefore live in shared memory.  A ray whose stack runs empty parks until the queue
+// has been drained (before the next refill), then stores its hit.
+constexpr int kQueueCap = 64;
+
+struct WarpShared {
+    float4   ray_a[32];      // ox, oy, oz, dx
+    float4   ray_b[32];      // dy, dz, tmin, -
+    uint32_t hit_t[32];      // float bits of the closest t so far (atomicMin target)
+    float    hit_u[32], hit_v[32];
+    int32_t  hit_prim[32];
+    uint32_t queue[kQueueCap];   // owner lane << 27 | triangle block index
+};
+
+__device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, unsigned lane, uint32_t &qn, uint32_t k)
+{
+    __syncwarp();
+    bool cand = false;
+    uint32_t owner = 0, tbits = 0, prim = 0;
+    float u = 0.0f, v = 0.0f;
+    if (lane < k) {
+        const uint32_t e = ws.queue[qn - k + lane];
+        owner = e >> 27;
+        const uint4 *tp = bvh.blocks + (size_t)(e & 0x07ffffffu) * 4;
+        uint4 ta, tb, tc, td;
+        ld_block_half(tp, ta, tb); ld_block_half(tp + 2, tc, td);
+        const float4 ra = ws.ray_a[owner], rb = ws.ray_b[owner];
+        RayCtx r;
+        r.ox = ra.x; r.oy = ra.y; r.oz = ra.z; r.dx = ra.w; r.dy = rb.x; r.dz = rb.y; r.tmin = rb.z;
+        float t = __uint_as_float(ws.hit_t[owner]);
+        if (tri_hit(as_f4(ta), as_f4(tb), as_f4(tc), r, t, u, v)) {
+            cand = true; tbits = __float_as_uint(t); prim = td.x;
+            atomicMin(&ws.hit_t[owner], tbits);
+        }
+    }
+    __syncwarp();
+    if (cand && ws.hit_t[owner] == tbits) { ws.hit_u[owner] = u; ws.hit_v[owner] = v; ws.hit_prim[owner] = (int32_t)prim; }
+    __syncwarp();
+    qn -= k;
+}
+
+template <class IO, int FETCH_THRESHOLD>
+__global__ void __launch_bounds__(kTraceBlock, 6)
+trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
+         uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
+{
+    __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+    __shared__ uint8_t perm_lut[8 * 128];
+    __shared__ WarpShared wsh[kTraceBlock / 32];
+    for (uint32_t i = threadIdx.x; i < 8u * 128u; i += kTraceBlock) perm_lut[i] = (uint8_t)perm8(i & 127u, i >> 7);
+    __syncthreads();
+    const uint32_t n = n_ptr ? *n_ptr : n_static;
+    if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
+    const unsigned lane = threadIdx.x & 31u;
+    WarpShared &ws = wsh[threadIdx.x >> 5];
+    uint2 *const my = sstack + threadIdx.x;
+    uint2 lstack[kStackSize - kSmemStack];
+    int sp = 0;
+
+    // state: 0 = idle, 1 = traversing, 2 = parked (stack empty, waiting for the queue to drain)
+    int state = 0;
+    bool exhausted = false;
+    uint32_t ray_i = 0, qn = 0;
+    const uint8_t *lut = perm_lut;
+    RayCtx r;
+    uint2 G;
+    G.x = G.y = 0u;
+    r = make_ray(0.f, 0.f, 0.f, 0.f, 0.f, 1.f, 0.f);
+
+    for (;;) {
+        const unsigned act = __ballot_sync(0xffffffffu, state == 1);
+        if (__popc(act) < (FETCH_THRESHOLD > 0 ? FETCH_THRESHOLD : 1)) {
+            // drain the queue so that parked rays are final, store them, then refill
+            while (qn) flush_queue(bvh, ws, lane, qn, qn < 32u ? qn : 32u);
+            if (state == 2) {
+                io.store(ray_i, ws.hit_prim[lane], __uint_as_float(ws.hit_t[lane]), ws.hit_u[lane], ws.hit_v[lane]);
+                state = 0;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~act;
+                const int cnt = __popc(idle);
+                const int leader = __ffs(idle) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)cnt);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (base + (uint32_t)cnt >= n) exhausted = true;
+                if (state == 0) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                    float ox, oy, oz, dx, dy, dz, t0, t1;
+                    if (i < n && io.load(i, ox, oy, oz, dx, dy, dz, t0, t1)) {
+                        r = make_ray(ox, oy, oz, dx, dy, dz, t0);
+                        lut = perm_lut + r.oct_inv * 128u;
+                        ws.ray_a[lane] = make_float4(ox, oy, oz, dx);
+                        ws.ray_b[lane] = make_float4(dy, dz, t0, 0.0f);
+                        ws.hit_t[lane] = __float_as_uint(t1);
+                        ws.hit_prim[lane] = -1;
+                        G.x = 0u; G.y = 0x01000000u;
+                        sp = 0;
+                        ray_i = i;
+                        state = 1;
+                    }
+                }
+                if (!__any_sync(0xffffffffu, state == 1)) {
+                    if (exhausted) break;
+                    continue;
+                }
+            } else if (act == 0u) {
+                break;
+            }
+        }
+        uint32_t T = 0, tri0 = 0;
+        if (state == 1) {
+            // next internal child, front to back: highest pending priority bit
+            const int bit = 31 - __clz((int)G.y);
+            G.y ^= 1u << bit;
+            if (G.y >> 24) {
+                if (sp < kSmemStack) my[sp * kTraceBlock] = G; else lstack[sp - kSmemStack] = G;
+                sp++;
+            }
+            const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
+            const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
+            const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
+            uint4 q0, q1, q2, q3;
+            ld_block_half(np, q0, q1); ld_block_half(np + 2, q2, q3);
+            const uint32_t h7 = node_hits7(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
+            const uint32_t imask = q2.w >> 24;
+            G.x = q0.w;
+            G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
+            T = leaf_tri_mask(h7 & ~imask, (q3.y >> 24) | ((q3.w >> 24) << 8));
+            tri0 = q0.w + (uint32_t)__popc(imask);
+            if (!(G.y >> 24)) {
+                if (sp == 0) {
+                    state = 2;
+                } else {
+                    sp--;
+                    G = sp < kSmemStack ? my[sp * kTraceBlock] : lstack[sp - kSmemStack];
+                }
+            }
+        }
+        // ---- append this step's triangles to the warp queue, one per lane per round
+        for (;;) {
+            const bool has = T != 0u;
+            const unsigned b = __ballot_sync(0xffffffffu, has);
+            if (!b) break;
+            if (qn > (uint32_t)kQueueCap - 32u) flush_queue(bvh, ws, lane, qn, 32u);
+            if (has) {
+                const int tb = 31 - __clz((int)T);
+                T ^= 1u << tb;
+                ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = (lane << 27) | (tri0 + (uint32_t)tb);
+            }
+            qn += (uint32_t)__popc(b);
+        }
+        if (qn >= 32u) flush_queue(bvh, ws, lane, qn, 32u);
     }
 }
 
@@ -176,8 +339,7 @@ trace_simple(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr,
         const RayCtx r = make_ray(ox, oy, oz, dx, dy, dz, t0);
         LocalStack st;
         const Hit h = trace_ray(bvh, r, t1, st);
-        const int32_t prim = h.slot < 0 ? -1 : __ldg(bvh.prim_id + h.slot);
-        io.store(i, prim, h.t, h.u, h.v);
+        io.store(i, h.prim, h.t, h.u, h.v);
     }
 }
 
@@ -200,11 +362,26 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
         }
         per_sm = cached;
     }
-    const uint32_t blocks = (uint32_t)(num_sms * per_sm);
-    if (tune.variant == 2)
-        trace_persistent<IO, 0><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
-    else
+    if (tune.variant == 2) {
+        const uint32_t blocks = (uint32_t)(num_sms * per_sm);
         trace_persistent<IO, 20><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+        return;
+    }
+    if (tune.ctas_per_sm <= 0) {
+        static int cached_wq = 0;
+        if (!cached_wq) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cached_wq, trace_wq<IO, 20>, kTraceBlock, 0);
+            if (cached_wq <= 0) cached_wq = 4;
+        }
+        per_sm = cached_wq;
+    }
+    const uint32_t blocks = (uint32_t)(num_sms * per_sm);
+    if (tune.variant == 3)
+        trace_wq<IO, 26><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+    else if (tune.variant == 4)
+        trace_wq<IO, 14><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+    else
+        trace_wq<IO, 20><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
 }
 
 void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,

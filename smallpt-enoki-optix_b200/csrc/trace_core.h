@@ -8,12 +8,11 @@
 // (dependencies/embree/kernels/geometry/triangle_intersector_moeller.h:75-113): den != 0, U >= 0,
 // V >= 0, U+V <= |den|, |den|*tnear < T <= |den|*tfar.
 //
-// Instruction budget of the node test (sm_100a: the ALU pipe — PRMT/LOP3/SHF/SEL/FMNMX/FSETP —
-// issues at half the rate of the FMA pipe — FFMA/FMUL/IMAD — so ALU-pipe instructions are what is
-// minimised): per child 6 FFMA, 2 FMNMX3, 2 FMNMX, 1 FSET, 1 FFMA (mask accumulate); per child PAIR
-// 6 SEL (near/far by ray sign) and 6 IMAD.SHL (even child's planes); the odd child's planes are used
-// as floats as loaded (their low 16 bits are the sibling's plane: the builder rounds so that the
-// perturbation is conservative).
+// Instruction budget of the node test on sm_100a (measured, tools/mb/pipes.cu): PRMT/LOP3/SHF/SEL/
+// FSET/FMNMX3 share the ALU pipe at 0.5 warp-instr/clk/SMSP; FFMA (and 2-input FMNMX) issue at
+// 1/clk; IDP.4A and IMAD run on the heavy FMA pipe at 0.5/clk, beside the ALU pipe.  Per child:
+// 6 IDP.4A (plane byte -> float operand), 6 FFMA, 2 FMNMX3 + 2 FMNMX, 1 FSET, 1 FFMA (mask
+// accumulate); per node 12 SEL (near/far words by ray sign).
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -61,15 +60,24 @@ WPT_HD int pop_count(uint32_t x)
     return __builtin_popcount(x);
 #endif
 }
-// byte `i` (0..7) of the 64-bit value {hi,lo}
-WPT_HD uint32_t byte_of(uint32_t lo, uint32_t hi, uint32_t i)
+// d = c + sum of the four byte products of a and b (unsigned)
+WPT_HD uint32_t dp4a_u(uint32_t a, uint32_t b, uint32_t c)
 {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(lo, hi, i) & 0xffu;
+    return __dp4a(a, b, c);
 #else
-    return (uint32_t)((((uint64_t)hi << 32) | lo) >> (8 * i)) & 0xffu;
+    for (int i = 0; i < 4; i++) c += ((a >> (8 * i)) & 0xffu) * ((b >> (8 * i)) & 0xffu);
+    return c;
 #endif
 }
+// plane byte J of `word` as the float 256 + q/256 (bits 0x43800000 + 128 q): one IDP.4A, no ALU-pipe
+// instruction.  With A = 256*scale/d and B = (p-o)/d - 256*A:  fma(f, A, B) = (p + q*scale - o)/d.
+template <int J>
+WPT_HD float q2f(uint32_t word)
+{
+    return u2f(dp4a_u(word, 0x80u << (8 * J), 0x43800000u));
+}
+
 // permutation of the bit positions of an 8-bit mask by XOR with o: result bit (s ^ o) = m bit s.
 // Internal children are visited in order of decreasing (slot ^ oct_inv) — slot s holds the child
 // lying furthest towards corner s of the node, so that is front to back for the ray's octant.
@@ -103,45 +111,36 @@ WPT_HD RayCtx make_ray(float ox, float oy, float oz, float dx, float dy, float d
 }
 
 // ---------------------------------------------------------------- node test
-// n0 = (p.x, p.y, p.z, e|imask<<24); q[2*axis + side] = the four plane words of that axis/side.
-// Returns the 8-bit mask of children (slot order) whose box the ray segment [tmin, tmax] touches.
-WPT_HD uint32_t node_hits8(const uint4 n0, const uint4 qxl, const uint4 qxh, const uint4 qyl, const uint4 qyh,
-                           const uint4 qzl, const uint4 qzh, const RayCtx &r, float tmax)
+// q0 = (p.x, p.y, p.z, base); q1 = (xlo[0..3], xlo[4..7], xhi[0..3], xhi[4..7]); q2 likewise for y,
+// q3 for z.  Byte 7 of each array is header: xlo e[0]+8, xhi e[1]+8, ylo e[2]+8, yhi imask,
+// zlo / zhi triangle counts.  Returns the 7-bit mask of children (slot order) whose box the ray
+// segment [tmin, tmax] touches (empty slots hold an inverted box and never hit).
+WPT_HD uint32_t node_hits7(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3, const RayCtx &r,
+                           float tmax)
 {
-    const uint32_t e = n0.w;
-    const float ax = u2f((e & 0xffu) << 23) * r.ix;
-    const float ay = u2f(((e >> 8) & 0xffu) << 23) * r.iy;
-    const float az = u2f(((e >> 16) & 0xffu) << 23) * r.iz;
-    const float bx = (u2f(n0.x) - r.ox) * r.ix;
-    const float by = (u2f(n0.y) - r.oy) * r.iy;
-    const float bz = (u2f(n0.z) - r.oz) * r.iz;
+    const float ax = u2f((q1.y >> 24) << 23) * r.ix;     // 256 * scale / d
+    const float ay = u2f((q1.w >> 24) << 23) * r.iy;
+    const float az = u2f((q2.y >> 24) << 23) * r.iz;
+    const float bx = fmaf(-256.0f, ax, (u2f(q0.x) - r.ox) * r.ix);
+    const float by = fmaf(-256.0f, ay, (u2f(q0.y) - r.oy) * r.iy);
+    const float bz = fmaf(-256.0f, az, (u2f(q0.z) - r.oz) * r.iz);
     const bool px = r.ix >= 0.0f, py = r.iy >= 0.0f, pz = r.iz >= 0.0f;
+    const uint32_t xn[2] = { px ? q1.x : q1.z, px ? q1.y : q1.w }, xf[2] = { px ? q1.z : q1.x, px ? q1.w : q1.y };
+    const uint32_t yn[2] = { py ? q2.x : q2.z, py ? q2.y : q2.w }, yf[2] = { py ? q2.z : q2.x, py ? q2.w : q2.y };
+    const uint32_t zn[2] = { pz ? q3.x : q3.z, pz ? q3.y : q3.w }, zf[2] = { pz ? q3.z : q3.x, pz ? q3.w : q3.y };
     float acc = 8388608.0f;   // 2^23: the low mantissa bits collect the hit mask
-#define WPT_PAIR(J, W)                                                                             \
-    {                                                                                              \
-        const uint32_t xn = px ? qxl.W : qxh.W, xf = px ? qxh.W : qxl.W;                           \
-        const uint32_t yn = py ? qyl.W : qyh.W, yf = py ? qyh.W : qyl.W;                           \
-        const uint32_t zn = pz ? qzl.W : qzh.W, zf = pz ? qzh.W : qzl.W;                           \
-        {   /* even child: low halves */                                                           \
-            const float tx0 = fmaf(u2f(xn << 16), ax, bx), tx1 = fmaf(u2f(xf << 16), ax, bx);      \
-            const float ty0 = fmaf(u2f(yn << 16), ay, by), ty1 = fmaf(u2f(yf << 16), ay, by);      \
-            const float tz0 = fmaf(u2f(zn << 16), az, bz), tz1 = fmaf(u2f(zf << 16), az, bz);      \
-            const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                           \
-            const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                             \
-            acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(1 << (2 * J)), acc);                        \
-        }                                                                                          \
-        {   /* odd child: the words as they are */                                                 \
-            const float tx0 = fmaf(u2f(xn), ax, bx), tx1 = fmaf(u2f(xf), ax, bx);        \
-            const float ty0 = fmaf(u2f(yn), ay, by), ty1 = fmaf(u2f(yf), ay, by);        \
-            const float tz0 = fmaf(u2f(zn), az, bz), tz1 = fmaf(u2f(zf), az, bz);        \
-            const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                           \
-            const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                             \
-            acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(2 << (2 * J)), acc);                        \
-        }                                                                                          \
+#define WPT_CHILD(H, J)                                                                           \
+    {                                                                                             \
+        const float tx0 = fmaf(q2f<J>(xn[H]), ax, bx), tx1 = fmaf(q2f<J>(xf[H]), ax, bx);         \
+        const float ty0 = fmaf(q2f<J>(yn[H]), ay, by), ty1 = fmaf(q2f<J>(yf[H]), ay, by);         \
+        const float tz0 = fmaf(q2f<J>(zn[H]), az, bz), tz1 = fmaf(q2f<J>(zf[H]), az, bz);         \
+        const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                              \
+        const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                                \
+        acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(1 << (4 * H + J)), acc);                       \
     }
-    WPT_PAIR(0, x) WPT_PAIR(1, y) WPT_PAIR(2, z) WPT_PAIR(3, w)
-#undef WPT_PAIR
-    return f2u(acc) & 0xffu;
+    WPT_CHILD(0, 0) WPT_CHILD(0, 1) WPT_CHILD(0, 2) WPT_CHILD(0, 3) WPT_CHILD(1, 0) WPT_CHILD(1, 1) WPT_CHILD(1, 2)
+#undef WPT_CHILD
+    return f2u(acc) & 0x7fu;
 }
 
 // ---------------------------------------------------------------- triangle test
@@ -185,21 +184,12 @@ WPT_HD bool tri_hit(const float4 t0, const float4 t1, const float4 t2, const Ray
 
 // ---------------------------------------------------------------- one ray, start to finish
 struct Hit {
-    int32_t slot;   // leaf slot (index into tris / prim_id), -1 = miss
+    int32_t prim;   // original triangle index, -1 = miss
     float t, u, v;
 };
 
-WPT_HD uint4 ld_node(const uint4 *p)
-{
-#if defined(__CUDA_ARCH__)
-    return __ldg(p);
-#else
-    return *p;
-#endif
-}
-// one 256-bit load (sm_100a LDG.E.256): two consecutive 16-byte quads in a single L1 wavefront per
-// lane — divergent traversal is bound by L1 wavefronts per node visit, not by bytes
-WPT_HD void ld_node2(const uint4 *p, uint4 &a, uint4 &b)
+// one 256-bit load (sm_100a LDG.E.256): two consecutive 16-byte quads for ONE L1 wavefront per lane
+WPT_HD void ld_block_half(const uint4 *p, uint4 &a, uint4 &b)
 {
 #if defined(__CUDA_ARCH__)
     asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -209,57 +199,55 @@ WPT_HD void ld_node2(const uint4 *p, uint4 &a, uint4 &b)
     a = p[0]; b = p[1];
 #endif
 }
-WPT_HD float4 ld_tri(const float4 *p)
-{
-#if defined(__CUDA_ARCH__)
-    return __ldg(p);
-#else
-    return *p;
-#endif
-}
+WPT_HD float4 as_f4(const uint4 q) { float4 f; f.x = u2f(q.x); f.y = u2f(q.y); f.z = u2f(q.z); f.w = u2f(q.w); return f; }
 
-// triangle bit mask (bit i = triangle tri_base + i) of the leaf children in `leaf` (slot mask)
-WPT_HD uint32_t leaf_tri_mask(uint32_t leaf, uint32_t meta_lo, uint32_t meta_hi)
+// triangle bit mask (bit i = i-th triangle of the node) of the leaf children in `leaf` (slot mask);
+// cnt2 = the 2-bit triangle counts of slots 0..6
+WPT_HD uint32_t leaf_tri_mask(uint32_t leaf, uint32_t cnt2)
 {
     uint32_t T = 0;
     while (leaf) {
         const int s = high_bit(leaf);
         leaf ^= 1u << s;
-        const uint32_t m = byte_of(meta_lo, meta_hi, (uint32_t)s);
-        T |= (m >> 5) << (m & 31u);     // unary count << offset
+        const uint32_t below = cnt2 & ((1u << (2 * s)) - 1u);
+        const uint32_t off = (uint32_t)(pop_count(below & 0x1555u) + 2 * pop_count(below & 0x2aaau));
+        const uint32_t cnt = (cnt2 >> (2 * s)) & 3u;
+        T |= ((1u << cnt) - 1u) << off;
     }
     return T;
 }
 
-// Traversal entry: x = index of the first internal child of a node, y = (pending internal children,
-// permuted to visiting priority) << 24 | imask.  STACK must provide push(uint2) / pop() / empty().
+// Traversal entry: x = first child block of a node, y = (pending internal children, permuted to
+// visiting priority) << 24 | imask.  STACK must provide push(uint2) / pop() / empty().
 template <class STACK>
 WPT_HD Hit trace_ray(const BvhView &bvh, const RayCtx &r, float tmax, STACK &stack, uint64_t *counters = nullptr)
 {
     Hit hit;
-    hit.slot = -1; hit.t = tmax; hit.u = 0.0f; hit.v = 0.0f;
-    uint2 G; G.x = 0u; G.y = 0x01000000u;  // root: base 0, one pending child, imask 0 -> rel index 0
+    hit.prim = -1; hit.t = tmax; hit.u = 0.0f; hit.v = 0.0f;
+    uint2 G; G.x = 0u; G.y = 0x01000000u;  // root: block 0, one pending child, imask 0 -> rel index 0
     for (;;) {
         const int bit = high_bit(G.y);
         G.y ^= 1u << bit;
         if (G.y >> 24) stack.push(G);
         const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
         const uint32_t rel = (uint32_t)pop_count(G.y & ((1u << slot) - 1u) & 0xffu);
-        const uint4 *np = bvh.nodes + (size_t)(G.x + rel) * 8;
-        uint4 n0, n1, qxl, qxh, qyl, qyh, qzl, qzh;
-        ld_node2(np, n0, n1); ld_node2(np + 2, qxl, qxh); ld_node2(np + 4, qyl, qyh); ld_node2(np + 6, qzl, qzh);
-        const uint32_t h8 = node_hits8(n0, qxl, qxh, qyl, qyh, qzl, qzh, r, hit.t);
-        const uint32_t imask = n0.w >> 24;
-        G.x = n1.x;
-        G.y = (perm8(h8 & imask, r.oct_inv) << 24) | imask;
-        uint32_t T = leaf_tri_mask(h8 & ~imask, n1.z, n1.w);
+        const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
+        uint4 q0, q1, q2, q3;
+        ld_block_half(np, q0, q1); ld_block_half(np + 2, q2, q3);
+        const uint32_t h7 = node_hits7(q0, q1, q2, q3, r, hit.t);
+        const uint32_t imask = q2.w >> 24;
+        G.x = q0.w;
+        G.y = (perm8(h7 & imask, r.oct_inv) << 24) | imask;
+        uint32_t T = leaf_tri_mask(h7 & ~imask, (q3.y >> 24) | ((q3.w >> 24) << 8));
         if (counters) { counters[0]++; counters[1] += (uint64_t)pop_count(T); }
+        const uint32_t tri0 = q0.w + (uint32_t)pop_count(imask);
         while (T) {
             const int tb = high_bit(T);
             T ^= 1u << tb;
-            const uint32_t ti = n1.y + (uint32_t)tb;
-            const float4 *tp = bvh.tris + (size_t)ti * 3;
-            if (tri_hit(ld_tri(tp), ld_tri(tp + 1), ld_tri(tp + 2), r, hit.t, hit.u, hit.v)) hit.slot = (int32_t)ti;
+            const uint4 *tp = bvh.blocks + (size_t)(tri0 + (uint32_t)tb) * 4;
+            uint4 a, b, c, d;
+            ld_block_half(tp, a, b); ld_block_half(tp + 2, c, d);
+            if (tri_hit(as_f4(a), as_f4(b), as_f4(c), r, hit.t, hit.u, hit.v)) hit.prim = (int32_t)d.x;
         }
         if (!(G.y >> 24)) {
             if (stack.empty()) break;
