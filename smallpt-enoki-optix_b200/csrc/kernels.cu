@@ -180,32 +180,39 @@ struct WarpShared {
     uint32_t hit_t[32];      // float bits of the closest t so far (atomicMin target)
     float    hit_u[32], hit_v[32];
     int32_t  hit_prim[32];
-    uint32_t queue[kQueueCap];   // owner lane << 27 | triangle block index
+    uint2    queue[kQueueCap];   // one entry per hit LEAF: x = owner lane << 27 | first triangle block of the
+                                 // node, y = leaf slot << 16 | the node's 2-bit triangle counts
 };
 
+// every lane < k takes one queued leaf (1..3 triangles), tests it against its owner's ray and folds
+// the closest accepted hit into the owner's record
 __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, unsigned lane, uint32_t &qn, uint32_t k)
 {
     __syncwarp();
     bool cand = false;
-    uint32_t owner = 0, tbits = 0, prim = 0;
-    float u = 0.0f, v = 0.0f;
+    uint32_t owner = 0, prim = 0;
+    float t = 0.0f, u = 0.0f, v = 0.0f;
     if (lane < k) {
-        const uint32_t e = ws.queue[qn - k + lane];
-        owner = e >> 27;
-        const uint4 *tp = bvh.blocks + (size_t)(e & 0x07ffffffu) * 4;
-        uint4 ta, tb, tc, td;
-        ld_block_half(tp, ta, tb); ld_block_half(tp + 2, tc, td);
+        const uint2 e = ws.queue[qn - k + lane];
+        owner = e.x >> 27;
+        const uint32_t s2 = (e.y >> 16) * 2u, cnt2 = e.y & 0x3fffu;
+        const uint32_t below = cnt2 & ((1u << s2) - 1u);
+        const uint32_t off = (uint32_t)(__popc(below & 0x1555u) + 2 * __popc(below & 0x2aaau));
+        const uint32_t cnt = (cnt2 >> s2) & 3u;
+        const uint4 *tp = bvh.blocks + (size_t)((e.x & 0x07ffffffu) + off) * 4;
         const float4 ra = ws.ray_a[owner], rb = ws.ray_b[owner];
         RayCtx r;
         r.ox = ra.x; r.oy = ra.y; r.oz = ra.z; r.dx = ra.w; r.dy = rb.x; r.dz = rb.y; r.tmin = rb.z;
-        float t = __uint_as_float(ws.hit_t[owner]);
-        if (tri_hit(as_f4(ta), as_f4(tb), as_f4(tc), r, t, u, v)) {
-            cand = true; tbits = __float_as_uint(t); prim = td.x;
-            atomicMin(&ws.hit_t[owner], tbits);
+        t = __uint_as_float(ws.hit_t[owner]);
+        for (uint32_t j = 0; j < cnt; j++, tp += 4) {
+            uint4 ta, tb, tc, td;
+            ld_block_half(tp, ta, tb); ld_block_half(tp + 2, tc, td);
+            if (tri_hit(as_f4(ta), as_f4(tb), as_f4(tc), r, t, u, v)) { cand = true; prim = td.x; }
         }
+        if (cand) atomicMin(&ws.hit_t[owner], __float_as_uint(t));
     }
     __syncwarp();
-    if (cand && ws.hit_t[owner] == tbits) { ws.hit_u[owner] = u; ws.hit_v[owner] = v; ws.hit_prim[owner] = (int32_t)prim; }
+    if (cand && ws.hit_t[owner] == __float_as_uint(t)) { ws.hit_u[owner] = u; ws.hit_v[owner] = v; ws.hit_prim[owner] = (int32_t)prim; }
     __syncwarp();
     qn -= k;
 }
@@ -279,7 +286,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                 break;
             }
         }
-        uint32_t T = 0, tri0 = 0;
+        uint32_t L = 0, tri0 = 0, cnt2 = 0;   // hit leaf slots of this step
         if (state == 1) {
             // next internal child, front to back: highest pending priority bit
             const int bit = 31 - __clz((int)G.y);
@@ -297,7 +304,8 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const uint32_t imask = q2.w >> 24;
             G.x = q0.w;
             G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
-            T = leaf_tri_mask(h7 & ~imask, (q3.y >> 24) | ((q3.w >> 24) << 8));
+            L = h7 & ~imask;
+            cnt2 = (q3.y >> 24) | ((q3.w >> 24) << 8);
             tri0 = q0.w + (uint32_t)__popc(imask);
             if (!(G.y >> 24)) {
                 if (sp == 0) {
@@ -308,16 +316,16 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                 }
             }
         }
-        // ---- append this step's triangles to the warp queue, one per lane per round
+        // ---- append this step's hit leaves to the warp queue, one per lane per round
         for (;;) {
-            const bool has = T != 0u;
+            const bool has = L != 0u;
             const unsigned b = __ballot_sync(0xffffffffu, has);
             if (!b) break;
             if (qn > (uint32_t)kQueueCap - 32u) flush_queue(bvh, ws, lane, qn, 32u);
             if (has) {
-                const int tb = 31 - __clz((int)T);
-                T ^= 1u << tb;
-                ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = (lane << 27) | (tri0 + (uint32_t)tb);
+                const uint32_t sl = 31u - (uint32_t)__clz((int)L);
+                L ^= 1u << sl;
+                ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (sl << 16) | cnt2);
             }
             qn += (uint32_t)__popc(b);
         }
