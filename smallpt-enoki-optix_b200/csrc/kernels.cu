@@ -180,12 +180,12 @@ struct WarpShared {
     uint32_t hit_t[32];      // float bits of the closest t so far (atomicMin target)
     float    hit_u[32], hit_v[32];
     int32_t  hit_prim[32];
-    uint2    queue[kQueueCap];   // one entry per hit LEAF: x = owner lane << 27 | first triangle block of the
-                                 // node, y = leaf slot << 16 | the node's 2-bit triangle counts
+    uint2    queue[kQueueCap];   // one entry per node step that hit leaves: x = owner lane << 27 | first
+                                 // triangle block of the node, y = hit leaf slots << 16 | 2-bit triangle counts
 };
 
-// every lane < k takes one queued leaf (1..3 triangles), tests it against its owner's ray and folds
-// the closest accepted hit into the owner's record
+// every lane < k takes one queued entry (the leaves one node step hit, 1..3 triangles each), tests
+// them against the owner's ray and folds the closest accepted hit into the owner's record
 __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, unsigned lane, uint32_t &qn, uint32_t k)
 {
     __syncwarp();
@@ -195,19 +195,22 @@ __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, 
     if (lane < k) {
         const uint2 e = ws.queue[qn - k + lane];
         owner = e.x >> 27;
-        const uint32_t s2 = (e.y >> 16) * 2u, cnt2 = e.y & 0x3fffu;
-        const uint32_t below = cnt2 & ((1u << s2) - 1u);
-        const uint32_t off = (uint32_t)(__popc(below & 0x1555u) + 2 * __popc(below & 0x2aaau));
-        const uint32_t cnt = (cnt2 >> s2) & 3u;
-        const uint4 *tp = bvh.blocks + (size_t)((e.x & 0x07ffffffu) + off) * 4;
+        const uint32_t cnt2 = e.y & 0x3fffu;
+        uint32_t L = e.y >> 16;
         const float4 ra = ws.ray_a[owner], rb = ws.ray_b[owner];
         RayCtx r;
         r.ox = ra.x; r.oy = ra.y; r.oz = ra.z; r.dx = ra.w; r.dy = rb.x; r.dz = rb.y; r.tmin = rb.z;
         t = __uint_as_float(ws.hit_t[owner]);
-        for (uint32_t j = 0; j < cnt; j++, tp += 4) {
-            uint4 ta, tb, tc, td;
-            ld_block_half(tp, ta, tb); ld_block_half(tp + 2, tc, td);
-            if (tri_hit(as_f4(ta), as_f4(tb), as_f4(tc), r, t, u, v)) { cand = true; prim = td.x; }
+        // triangle bit mask of the hit leaves (bit i = i-th triangle of the node)
+        uint32_t T = leaf_tri_mask(L, cnt2);
+        const uint4 *t0p = bvh.blocks + (size_t)(e.x & 0x07ffffffu) * 4;
+        while (T) {
+            const int tb = 31 - __clz((int)T);
+            T ^= 1u << tb;
+            const uint4 *tp = t0p + (size_t)tb * 4;
+            uint4 ta, tb4, tc, td;
+            ld_block_half(tp, ta, tb4); ld_block_half(tp + 2, tc, td);
+            if (tri_hit(as_f4(ta), as_f4(tb4), as_f4(tc), r, t, u, v)) { cand = true; prim = td.x; }
         }
         if (cand) atomicMin(&ws.hit_t[owner], __float_as_uint(t));
     }
@@ -217,8 +220,19 @@ __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, 
     qn -= k;
 }
 
-template <class IO, int FETCH_THRESHOLD>
-__global__ void __launch_bounds__(kTraceBlock, 6)
+__device__ __forceinline__ void sts64(uint32_t addr, uint2 v)
+{
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+
+template <class IO, int FETCH_THRESHOLD, int MIN_CTAS>
+__global__ void __launch_bounds__(kTraceBlock, MIN_CTAS)
 trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
          uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
 {
@@ -231,9 +245,13 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
     if (live_acc && blockIdx.x == 0 && threadIdx.x == 0) *live_acc += n;
     const unsigned lane = threadIdx.x & 31u;
     WarpShared &ws = wsh[threadIdx.x >> 5];
-    uint2 *const my = sstack + threadIdx.x;
+    // traversal stack: a shared-memory byte address that moves by one row (kTraceBlock entries) per
+    // push / pop; entries beyond kSmemStack spill to local memory (deep trees only)
+    constexpr uint32_t kRow = kTraceBlock * (uint32_t)sizeof(uint2);
+    const uint32_t s_base = (uint32_t)__cvta_generic_to_shared(sstack + threadIdx.x);
+    const uint32_t s_limit = s_base + kSmemStack * kRow;
+    uint32_t s_top = s_base;
     uint2 lstack[kStackSize - kSmemStack];
-    int sp = 0;
 
     // state: 0 = idle, 1 = traversing, 2 = parked (stack empty, waiting for the queue to drain)
     int state = 0;
@@ -273,7 +291,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                         ws.hit_t[lane] = __float_as_uint(t1);
                         ws.hit_prim[lane] = -1;
                         G.x = 0u; G.y = 0x01000000u;
-                        sp = 0;
+                        s_top = s_base;
                         ray_i = i;
                         state = 1;
                     }
@@ -292,8 +310,8 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const int bit = 31 - __clz((int)G.y);
             G.y ^= 1u << bit;
             if (G.y >> 24) {
-                if (sp < kSmemStack) my[sp * kTraceBlock] = G; else lstack[sp - kSmemStack] = G;
-                sp++;
+                if (s_top < s_limit) sts64(s_top, G); else lstack[(s_top - s_limit) / kRow] = G;
+                s_top += kRow;
             }
             const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
             const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
@@ -308,28 +326,26 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             cnt2 = (q3.y >> 24) | ((q3.w >> 24) << 8);
             tri0 = q0.w + (uint32_t)__popc(imask);
             if (!(G.y >> 24)) {
-                if (sp == 0) {
+                if (s_top == s_base) {
                     state = 2;
                 } else {
-                    sp--;
-                    G = sp < kSmemStack ? my[sp * kTraceBlock] : lstack[sp - kSmemStack];
+                    s_top -= kRow;
+                    G = s_top < s_limit ? lds64(s_top) : lstack[(s_top - s_limit) / kRow];
                 }
             }
         }
-        // ---- append this step's hit leaves to the warp queue, one per lane per round
-        for (;;) {
+        // ---- append this step's hit leaves to the warp queue: ONE entry per lane (all its hit leaves)
+        {
             const bool has = L != 0u;
             const unsigned b = __ballot_sync(0xffffffffu, has);
-            if (!b) break;
-            if (qn > (uint32_t)kQueueCap - 32u) flush_queue(bvh, ws, lane, qn, 32u);
-            if (has) {
-                const uint32_t sl = 31u - (uint32_t)__clz((int)L);
-                L ^= 1u << sl;
-                ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (sl << 16) | cnt2);
+            if (b) {
+                if (qn > (uint32_t)kQueueCap - 32u) flush_queue(bvh, ws, lane, qn, 32u);
+                if (has)
+                    ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | cnt2);
+                qn += (uint32_t)__popc(b);
+                if (qn >= 32u) flush_queue(bvh, ws, lane, qn, 32u);
             }
-            qn += (uint32_t)__popc(b);
         }
-        if (qn >= 32u) flush_queue(bvh, ws, lane, qn, 32u);
     }
 }
 
@@ -375,21 +391,23 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
         trace_persistent<IO, 20><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
         return;
     }
-    if (tune.ctas_per_sm <= 0) {
-        static int cached_wq = 0;
-        if (!cached_wq) {
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cached_wq, trace_wq<IO, 20>, kTraceBlock, 0);
-            if (cached_wq <= 0) cached_wq = 4;
+    auto launch = [&](auto kern) {
+        int occ = tune.ctas_per_sm;
+        if (occ <= 0) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kTraceBlock, 0);
+            if (occ <= 0) occ = 4;
         }
-        per_sm = cached_wq;
+        kern<<<(uint32_t)(num_sms * occ), kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+    };
+    switch (tune.variant) {
+    case 3: launch(trace_wq<IO, 26, 6>); break;
+    case 4: launch(trace_wq<IO, 14, 6>); break;
+    case 5: launch(trace_wq<IO, 20, 8>); break;
+    case 6: launch(trace_wq<IO, 24, 8>); break;
+    case 7: launch(trace_wq<IO, 20, 7>); break;
+    case 8: launch(trace_wq<IO, 20, 6>); break;
+    default: launch(trace_wq<IO, 20, 7>); break;
     }
-    const uint32_t blocks = (uint32_t)(num_sms * per_sm);
-    if (tune.variant == 3)
-        trace_wq<IO, 26><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
-    else if (tune.variant == 4)
-        trace_wq<IO, 14><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
-    else
-        trace_wq<IO, 20><<<blocks, kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
 }
 
 void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,
