@@ -53,11 +53,12 @@ def workload(name, scale=1.0):
 
 def alg_bytes(n_tris):
     """Algorithmic bytes per ray segment (SURVEY §8d's formula with this layout):
-    one root->leaf descent of D = ceil(log8(T/3)) 80-byte nodes + one 3-triangle leaf of 48-byte blocks,
-    plus the SoA record streams each kernel must move."""
-    D = int(np.ceil(np.log(max(n_tris / 3.0, 8.0)) / np.log(8.0)))
-    trav = D * 80 + 3 * 48
-    trace = 32 + 16 + 4 + trav            # read (o,d) 2x16 B, write hit 16 B, prim id 4 B
+    one root->leaf descent of D = ceil(log7(T/3)) 64-byte 7-wide nodes + one 3-triangle leaf of 64-byte
+    blocks (the primitive id travels in the triangle block), plus the SoA record streams each kernel
+    must move."""
+    D = int(np.ceil(np.log(max(n_tris / 3.0, 7.0)) / np.log(7.0)))
+    trav = D * 64 + 3 * 64
+    trace = 32 + 16 + trav                # read (o,d) 2x16 B, write hit 16 B
     shade = 40 + 16 + 48 + 40             # read ray 40 + hit 16 + attributes 48, write next ray 40
     return dict(D=D, trav=trav, trace=trace, shade=shade, pipeline=trace + shade)
 
@@ -275,7 +276,7 @@ def run_ours(args):
         n_trace = pst["passes"] * depth
         trace_s = pst["ms_trace"] * 1e-3
         achieved = pst["segments"] * ab["trace"] / trace_s / 1e9
-        roof = {"bound": "hbm", "kernel": "trace_persistent", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": "trace_wq", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "peak_source": which, "traffic": None,
                 "alg_bytes_per_ray": ab["trace"], "rays_per_launch": pst["segments"] / n_trace,
                 "avg_launch_ms": pst["ms_trace"] / n_trace, "launches": n_trace,
