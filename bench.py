@@ -63,6 +63,16 @@ def alg_bytes(n_tris):
     return dict(D=D, trav=trav, trace=trace, shade=shade, pipeline=trace + shade)
 
 
+def traffic_per_launch(rays_per_launch):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/r1_trace_traffic.json: measured bytes per ray x the rays one launch processes)"""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r1_trace_traffic.json")))
+        return float(t["dram_bytes_per_ray_weighted"]) * rays_per_launch
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -137,8 +147,8 @@ def run_reference(args):
     import scenes
     gen, W, H, spp, depth = workload(args.workload)
     sd = gen()
-    # bounded sample: the full frame at 1 spp per step (C3: ~5 M segments, seconds on 8 cores)
-    sample_spp = 1
+    # bounded sample: the full frame at 16 spp per step (C3: ~85 M segments, ~2 s on 16 cores)
+    sample_spp = min(16, spp)
     times, segs = [], 0
     kind, cores = "port", 1
     for i in range(args.warmup + args.steps):
@@ -277,7 +287,7 @@ def run_ours(args):
         trace_s = pst["ms_trace"] * 1e-3
         achieved = pst["segments"] * ab["trace"] / trace_s / 1e9
         roof = {"bound": "hbm", "kernel": "trace_wq", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "peak_source": which, "traffic": None,
+                "frac": achieved / peak, "peak_source": which, "traffic": traffic_per_launch(pst["segments"] / n_trace),
                 "alg_bytes_per_ray": ab["trace"], "rays_per_launch": pst["segments"] / n_trace,
                 "avg_launch_ms": pst["ms_trace"] / n_trace, "launches": n_trace,
                 "trace_mrays_s": pst["segments"] / trace_s / 1e6,
@@ -291,9 +301,11 @@ def run_ours(args):
     # ---- CPU baseline beside it (rank 0, N=1 only; bounded sample)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, 1, 0)
+        mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, 1, 0)      # calibrate
+        k = int(max(1, min(spp, round(12.0 / max(dt, 1e-3)))))                       # ~12 s of CPU work
+        mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, k, 0)
         cpu = {"value": mr, "unit": "Mrays/s", "cores": cores, "kind": kind,
-               "sample": f"same scene/camera, {W}x{H}, depth {depth}, 1 spp of {spp} ({seg} segments, {dt:.1f} s)"}
+               "sample": f"same scene/camera, {W}x{H}, depth {depth}, {k} spp of {spp} ({seg} segments, {dt:.1f} s)"}
 
     if rank == 0:
         line = {"metric": "Mrays/s (all bounces, device-timed)", "value": value, "unit": "Mrays/s", "n_gpus": world,
