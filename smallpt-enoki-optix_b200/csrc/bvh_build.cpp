@@ -7,6 +7,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -15,9 +16,11 @@ namespace wpt {
 namespace {
 
 constexpr float kInf = std::numeric_limits<float>::infinity();
-constexpr int   kBins = 16;
+constexpr int   kBins = 32;
 constexpr float kCostNode = 1.0f;  // c_n
-constexpr float kCostTri = 0.3f;   // c_p
+// c_p: cost of one triangle relative to a node step; WPT_COST_TRI overrides it (tuning knob, tools/bvh_stats.py)
+static float cost_tri_init() { const char *e = std::getenv("WPT_COST_TRI"); return e ? (float)std::atof(e) : 0.3f; }
+static const float kCostTri = cost_tri_init();
 
 struct Box {
     float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};

@@ -11,7 +11,7 @@ using namespace wpt;
 
 extern "C" {
 
-// returns 0 ok; fills stats[0..5] = n_nodes, n_tris, max_depth, sah_cost, build_ms, n_problems
+// returns 0 ok; fills stats[0..7] = n_nodes, n_tris, max_depth, sah_cost, build_ms, n_problems, n_children, n_leaves
 int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris, double *stats)
 {
     BuiltBvh b;
@@ -77,6 +77,14 @@ int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uin
         }
         for (int k = 0; k < 3; k++) { lo_of[3 * n + k] = nlo[k]; hi_of[3 * n + k] = nhi[k]; }
     }
+    double n_children = 0, n_leaves = 0;
+    for (uint32_t n : order)
+        for (int sl = 0; sl < kWidth; sl++) {
+            if (node_slot_empty(b.blocks[n].node, sl)) continue;
+            n_children++;
+            if (!(node_imask(b.blocks[n].node) & (1u << sl))) n_leaves++;
+        }
+    stats[6] = n_children; stats[7] = n_leaves;
     for (uint32_t i = 0; i < n_tris; i++) if (seen[i] != 1) problems++;
     for (int r : block_refs) if (r != 1) problems++;
     if (order.size() != b.n_nodes || b.n_tris != n_tris) problems++;

@@ -406,6 +406,7 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 6: launch(trace_wq<IO, 24, 8>); break;
     case 7: launch(trace_wq<IO, 20, 7>); break;
     case 8: launch(trace_wq<IO, 20, 6>); break;
+
     default: launch(trace_wq<IO, 20, 7>); break;
     }
 }

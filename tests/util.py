@@ -28,10 +28,10 @@ def random_rays(sd, n, seed, inside=True):
 
 
 def hosttest_build(H, sd):
-    st = (C.c_double * 6)()
+    st = (C.c_double * 8)()
     rc = H.wpt_hosttest_build(sd.pos.ctypes.data_as(C.c_void_p), C.c_uint32(sd.pos.shape[0]),
                               sd.idx.ctypes.data_as(C.c_void_p), C.c_uint32(sd.n_tris), st)
-    return rc, dict(n_nodes=st[0], n_tris=st[1], max_depth=st[2], sah=st[3], build_ms=st[4], problems=st[5])
+    return rc, dict(n_nodes=st[0], n_tris=st[1], max_depth=st[2], sah=st[3], build_ms=st[4], problems=st[5], children=st[6], leaves=st[7])
 
 
 def hosttest_trace(H, sd, o, d, tmin=1e-3, tmax=1e20):
