@@ -133,7 +133,14 @@ def cpu_reference_run(sd, W, H, depth, spp, budget_s, threads=0):
     c = sd.camera
     cam = O.camera(c["look_from"], c["look_at"], c["up"], fov_y=c["fov_y"])
     m.backend(backend)  # build the CPU BVH outside the timed region (the reference does not time commit either)
-    cores = O.lib().orc_num_threads() if threads <= 0 else threads
+    if threads <= 0:
+        # all host cores this process may use; torchrun exports OMP_NUM_THREADS=1, which must not
+        # shrink the CPU arm to one thread
+        try:
+            threads = len(os.sched_getaffinity(0))
+        except AttributeError:
+            threads = os.cpu_count() or 1
+    cores = threads
     t0 = time.perf_counter()
     film, seg = m.render(backend, cam, W, H, 0, spp, depth, rng_mode=O.RNG_PCG32, threads=threads)
     dt = time.perf_counter() - t0

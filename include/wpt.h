@@ -3,8 +3,8 @@
  * per-bounce hot path.  Plain pointers and sizes only; no C++/torch types cross this boundary.
  * Every entry point returns 0 on success or a WPT_E_* code; wpt_last_error() gives the text
  * (thread-local).  Nothing throws across the ABI (the reference throws std::runtime_error from
- * OPTIX_CHECK/CUDA_CHECK, src/accel/optix_backend.h:25-82 — the C++ shim in
- * smallpt-enoki-optix_b200/src/wpt_shim.h re-raises our codes the same way).
+ * OPTIX_CHECK/CUDA_CHECK, src/accel/optix_backend.h:25-82 — the C++ shim include/wpt_shim.hpp
+ * re-raises our codes the same way).
  *
  * All file:line citations are relative to the reference tree (/root/reference).
  *
@@ -69,6 +69,24 @@ int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
 int  wpt_scene_commit(wpt_scene *s, int device);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
 void wpt_scene_destroy(wpt_scene *s);
+
+/* ------------------------------------------------------------------ OBJ / MTL ingestion
+ * Replaces load_meshes (src/main.cpp:133-251): tinyobjloader with triangulate = true, all shapes
+ * flattened into one pool, tri_id = global face index in file order (src/main.cpp:165-188),
+ * material_id = tinyobj id + 1 with id 0 the default white material (src/main.cpp:185,229-234).
+ * use_kd == 0 reproduces the reference as shipped (every material white, src/main.cpp:244);
+ * use_kd != 0 gives each material its MTL Kd colour (the commented-out intent, src/main.cpp:239-242).
+ * wpt_obj_mesh fills a wpt_mesh_desc whose pointers stay valid until wpt_obj_free; faces without
+ * normals carry normal index -1 (geometric-normal fallback, see above).  Texture coordinates are
+ * loaded like the reference does (src/main.cpp:215-223) and exposed, but nothing on the path reads
+ * them (the reference's textures are constant 1x1, src/main.cpp:40-44). */
+typedef struct wpt_obj wpt_obj;
+int  wpt_obj_load(const char *path, int use_kd, wpt_obj **out);
+int  wpt_obj_mesh(const wpt_obj *o, wpt_mesh_desc *out);
+int  wpt_obj_texcoords(const wpt_obj *o, const float **uvs, const int32_t **uv_triplets, uint32_t *n_uvs);
+/* name of material i in [0, n_materials): "" for the default material 0 */
+const char *wpt_obj_material_name(const wpt_obj *o, uint32_t i);
+void wpt_obj_free(wpt_obj *o);
 
 /* ------------------------------------------------------------------ closest-hit on ray streams
  * Replaces OptixBackend::intersect's launch (src/accel/optix_backend.h:422-460) and the device

@@ -78,6 +78,34 @@ def ref():
     return _ref
 
 
+def ref_obj_available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "libtinyobj_ref.so"))
+
+
+def ref_load_obj(path):
+    """The reference's own loader chain: its vendored tinyobjloader flattened like load_meshes
+    (src/main.cpp:143-223), through oracle/_ref/libtinyobj_ref.so (tinyobj_ref_wrap.cpp)."""
+    L = C.CDLL(os.path.join(_HERE, "_ref", "libtinyobj_ref.so"))
+    L.tor_load.restype = C.c_void_p
+    L.tor_counts.argtypes = [C.c_void_p, C.c_void_p]
+    L.tor_copy.argtypes = [C.c_void_p] * 9
+    L.tor_free.argtypes = [C.c_void_p]
+    h = L.tor_load(str(path).encode())
+    if not h:
+        raise RuntimeError(f"tinyobjloader failed on {path}")
+    cnt = (C.c_uint32 * 5)()
+    L.tor_counts(h, cnt)
+    V, Vn, Vt, T, M = [int(x) for x in cnt]
+    out = {"positions": np.zeros((V, 3), np.float32), "normals": np.zeros((Vn, 3), np.float32),
+           "texcoords": np.zeros((Vt, 2), np.float32), "kd": np.zeros((M, 3), np.float32),
+           "position_triplets": np.zeros((T, 3), np.int32), "normal_triplets": np.zeros((T, 3), np.int32),
+           "texcoord_triplets": np.zeros((T, 3), np.int32), "material_id": np.zeros(T, np.int32)}
+    L.tor_copy(h, *[out[k].ctypes.data for k in ("positions", "normals", "texcoords", "kd", "position_triplets",
+                                                 "normal_triplets", "texcoord_triplets", "material_id")])
+    L.tor_free(h)
+    return out
+
+
 def _c(a, dt):
     return np.ascontiguousarray(a, dtype=dt)
 

@@ -11,6 +11,7 @@
 #include "../../include/wpt.h"
 #include "bvh_build.h"
 #include "kernels.cuh"
+#include "obj_load.h"
 
 using namespace wpt;
 
@@ -178,6 +179,72 @@ extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
     *out = s->stats;
     return WPT_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// OBJ / MTL ingestion (src/main.cpp:133-251)
+struct wpt_obj {
+    ObjMesh mesh;
+    std::vector<float> albedo;   // 3 * (1 + M): default material first (src/main.cpp:229-234)
+};
+
+extern "C" int wpt_obj_load(const char *path, int use_kd, wpt_obj **out)
+{
+    if (!path || !out) return fail(WPT_E_INVALID, "wpt_obj_load: null argument");
+    wpt_obj *o = new (std::nothrow) wpt_obj();
+    if (!o) return fail(WPT_E_INVALID, "out of host memory");
+    std::string err;
+    if (!load_obj(path, o->mesh, err)) {
+        delete o;
+        return fail(err.rfind("cannot open", 0) == 0 ? WPT_E_IO : WPT_E_INVALID, "wpt_obj_load: " + err);
+    }
+    if (o->mesh.material_id.empty()) {
+        delete o;
+        return fail(WPT_E_INVALID, std::string("wpt_obj_load: no faces in ") + path);
+    }
+    const size_t M = o->mesh.material_names.size();
+    o->albedo.assign(3 * (M + 1), 1.0f);                       // src/main.cpp:234,244: Spectrum(1.0)
+    if (use_kd)
+        for (size_t k = 0; k < 3 * M; k++) o->albedo[3 + k] = o->mesh.kd[k];   // src/main.cpp:239-242
+    *out = o;
+    return WPT_OK;
+}
+
+extern "C" int wpt_obj_mesh(const wpt_obj *o, wpt_mesh_desc *d)
+{
+    if (!o || !d) return fail(WPT_E_INVALID, "wpt_obj_mesh: null argument");
+    const ObjMesh &m = o->mesh;
+    std::memset(d, 0, sizeof *d);
+    d->positions = m.positions.data();
+    d->position_triplets = m.position_triplets.data();
+    d->n_positions = (uint32_t)(m.positions.size() / 3);
+    d->n_triangles = (uint32_t)m.material_id.size();
+    if (!m.normals.empty()) {
+        d->normals = m.normals.data();
+        d->normal_triplets = m.normal_triplets.data();
+        d->n_normals = (uint32_t)(m.normals.size() / 3);
+    }
+    d->material_id = m.material_id.data();
+    d->albedo = o->albedo.data();
+    d->n_materials = (uint32_t)(o->albedo.size() / 3);
+    return WPT_OK;
+}
+
+extern "C" int wpt_obj_texcoords(const wpt_obj *o, const float **uvs, const int32_t **uv_triplets, uint32_t *n_uvs)
+{
+    if (!o || !uvs || !uv_triplets || !n_uvs) return fail(WPT_E_INVALID, "wpt_obj_texcoords: null argument");
+    *uvs = o->mesh.texcoords.data();
+    *uv_triplets = o->mesh.texcoord_triplets.data();
+    *n_uvs = (uint32_t)(o->mesh.texcoords.size() / 2);
+    return WPT_OK;
+}
+
+extern "C" const char *wpt_obj_material_name(const wpt_obj *o, uint32_t i)
+{
+    if (!o || i == 0 || i > o->mesh.material_names.size()) return "";
+    return o->mesh.material_names[i - 1].c_str();
+}
+
+extern "C" void wpt_obj_free(wpt_obj *o) { delete o; }
 
 // ------------------------------------------------------------------------------------------------
 static TraceTuning g_default_tune = {0, 0};

@@ -231,7 +231,7 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr)
     return v;
 }
 
-template <class IO, int FETCH_THRESHOLD, int MIN_CTAS>
+template <class IO, int FETCH_THRESHOLD, int MIN_CTAS, bool PACKED = false>
 __global__ void __launch_bounds__(kTraceBlock, MIN_CTAS)
 trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
          uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
@@ -318,7 +318,8 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
             uint4 q0, q1, q2, q3;
             ld_block_half(np, q0, q1); ld_block_half(np + 2, q2, q3);
-            const uint32_t h7 = node_hits7(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
+            const uint32_t h7 = PACKED ? node_hits7_p(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]))
+                                       : node_hits7(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
             const uint32_t imask = q2.w >> 24;
             G.x = q0.w;
             G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
@@ -406,6 +407,8 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 6: launch(trace_wq<IO, 24, 8>); break;
     case 7: launch(trace_wq<IO, 20, 7>); break;
     case 8: launch(trace_wq<IO, 20, 6>); break;
+    case 9: launch(trace_wq<IO, 20, 7, true>); break;
+    case 10: launch(trace_wq<IO, 20, 6, true>); break;
 
     default: launch(trace_wq<IO, 20, 7>); break;
     }

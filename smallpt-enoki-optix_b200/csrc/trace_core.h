@@ -143,6 +143,61 @@ WPT_HD uint32_t node_hits7(const uint4 q0, const uint4 q1, const uint4 q2, const
     return f2u(acc) & 0x7fu;
 }
 
+#if defined(__CUDACC__)
+// ---------------------------------------------------------------- node test, packed fp32 (device only)
+// sm_100a FFMA2 (fma.rn.f32x2): two IEEE fp32 FMAs per issued instruction — bit-identical results to
+// node_hits7, 21 issue slots instead of 42 for the plane distances (measured, tools/mb/pipes2.cu:
+// FFMA2 issues at half rate on the pipe IDP.4A uses, so it trades pipe cycles for issue slots, and
+// the traversal is issue bound).  Pairs: (x,y) of the near planes, (x,y) of the far planes, and
+// (z near, z far) of one child.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 p, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t node_hits7_p(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3,
+                                                 const RayCtx &r, float tmax)
+{
+    const float ax = u2f((q1.y >> 24) << 23) * r.ix;     // 256 * scale / d
+    const float ay = u2f((q1.w >> 24) << 23) * r.iy;
+    const float az = u2f((q2.y >> 24) << 23) * r.iz;
+    const float bx = fmaf(-256.0f, ax, (u2f(q0.x) - r.ox) * r.ix);
+    const float by = fmaf(-256.0f, ay, (u2f(q0.y) - r.oy) * r.iy);
+    const float bz = fmaf(-256.0f, az, (u2f(q0.z) - r.oz) * r.iz);
+    const f32x2 Axy = pack2(ax, ay), Bxy = pack2(bx, by), Azz = pack2(az, az), Bzz = pack2(bz, bz);
+    const bool px = r.ix >= 0.0f, py = r.iy >= 0.0f, pz = r.iz >= 0.0f;
+    const uint32_t xn[2] = { px ? q1.x : q1.z, px ? q1.y : q1.w }, xf[2] = { px ? q1.z : q1.x, px ? q1.w : q1.y };
+    const uint32_t yn[2] = { py ? q2.x : q2.z, py ? q2.y : q2.w }, yf[2] = { py ? q2.z : q2.x, py ? q2.w : q2.y };
+    const uint32_t zn[2] = { pz ? q3.x : q3.z, pz ? q3.y : q3.w }, zf[2] = { pz ? q3.z : q3.x, pz ? q3.w : q3.y };
+    float acc = 8388608.0f;
+#define WPT_CHILD(H, J)                                                                           \
+    {                                                                                             \
+        float tx0, ty0, tx1, ty1, tz0, tz1;                                                       \
+        unpack2(fma2(pack2(q2f<J>(xn[H]), q2f<J>(yn[H])), Axy, Bxy), tx0, ty0);                   \
+        unpack2(fma2(pack2(q2f<J>(xf[H]), q2f<J>(yf[H])), Axy, Bxy), tx1, ty1);                   \
+        unpack2(fma2(pack2(q2f<J>(zn[H]), q2f<J>(zf[H])), Azz, Bzz), tz0, tz1);                   \
+        const float tn = fmaxf(fmaxf(tx0, ty0), fmaxf(tz0, r.tmin));                              \
+        const float tf = fminf(fminf(tx1, ty1), fminf(tz1, tmax));                                \
+        acc = fmaf(tn <= tf ? 1.0f : 0.0f, (float)(1 << (4 * H + J)), acc);                       \
+    }
+    WPT_CHILD(0, 0) WPT_CHILD(0, 1) WPT_CHILD(0, 2) WPT_CHILD(0, 3) WPT_CHILD(1, 0) WPT_CHILD(1, 1) WPT_CHILD(1, 2)
+#undef WPT_CHILD
+    return f2u(acc) & 0x7fu;
+}
+#endif
+
 // ---------------------------------------------------------------- triangle test
 // t0 = (v0.xyz, e1.x) t1 = (e1.yz, e2.xy) t2 = (e2.z, Ng.xyz).  On accept updates tmax,u,v.
 // Like Embree (triangle_intersector_moeller.h:109-113, rcp = approximation + one Newton step) the

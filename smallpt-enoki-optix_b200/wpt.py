@@ -77,6 +77,10 @@ def lib():
             raise WptError(-1, f"{LIB_PATH} not built: run __graft_entry__.build() or make -C smallpt-enoki-optix_b200")
         L = C.CDLL(LIB_PATH)
         L.wpt_last_error.restype = C.c_char_p
+        L.wpt_obj_free.argtypes = [C.c_void_p]
+        L.wpt_obj_mesh.argtypes = [C.c_void_p, C.c_void_p]
+        L.wpt_obj_texcoords.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.wpt_obj_material_name.argtypes = [C.c_void_p, C.c_uint32]
         _lib = L
     return _lib
 
@@ -124,6 +128,55 @@ class ThinlensCamera:
     def reference_default(cls):
         """the camera main() builds, src/main.cpp:383"""
         return cls((0.0, 3.03, 5.0), (0.0, 0.03, 0.0), (0.0, 1.0, 0.0), 0.0, 1.0, 40.0 / 180.0 * np.pi)
+
+
+def load_meshes(path, use_kd=False):
+    """load_meshes (src/main.cpp:133-251) through wpt_obj_load.  Returns a dict of host numpy arrays:
+    position_triplets (T,3) i32, positions (V,3) f32, normal_triplets (T,3), normals (Vn,3),
+    texcoord_triplets (T,3), texcoords (Vt,2), material_id (T,) [tinyobj id + 1], albedo (M+1,3)
+    [all white unless use_kd], material_names."""
+    L = lib()
+    h = C.c_void_p()
+    _check(L.wpt_obj_load(str(path).encode(), C.c_int(1 if use_kd else 0), C.byref(h)))
+    try:
+        d = MeshDesc()
+        _check(L.wpt_obj_mesh(h, C.byref(d)))
+        T, V, Vn, M = d.n_triangles, d.n_positions, d.n_normals, d.n_materials
+
+        def arr(ptr, n, ct, dt):
+            if not ptr or n == 0:
+                return np.zeros(0, dt)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=(n,)).astype(dt, copy=True)
+
+        uv, uvt, nuv = C.c_void_p(), C.c_void_p(), C.c_uint32()
+        _check(L.wpt_obj_texcoords(h, C.byref(uv), C.byref(uvt), C.byref(nuv)))
+        L.wpt_obj_material_name.restype = C.c_char_p
+        out = {
+            "position_triplets": arr(d.position_triplets, 3 * T, C.c_int32, np.int32).reshape(-1, 3),
+            "positions": arr(d.positions, 3 * V, C.c_float, np.float32).reshape(-1, 3),
+            "normal_triplets": (arr(d.normal_triplets, 3 * T, C.c_int32, np.int32).reshape(-1, 3) if Vn
+                                else np.full((T, 3), -1, np.int32)),
+            "normals": arr(d.normals, 3 * Vn, C.c_float, np.float32).reshape(-1, 3),
+            "texcoord_triplets": arr(uvt.value, 3 * T, C.c_int32, np.int32).reshape(-1, 3),
+            "texcoords": arr(uv.value, 2 * nuv.value, C.c_float, np.float32).reshape(-1, 2),
+            "material_id": arr(d.material_id, T, C.c_int32, np.int32),
+            "albedo": arr(d.albedo, 3 * M, C.c_float, np.float32).reshape(-1, 3),
+            "material_names": [L.wpt_obj_material_name(h, C.c_uint32(i)).decode() for i in range(M)],
+        }
+    finally:
+        L.wpt_obj_free(h)
+    return out
+
+
+def scene_from_obj(path, device=0, use_kd=False):
+    """main()'s load_meshes -> Scene::add_triangle_mesh -> commit (src/main.cpp:362-366)"""
+    m = load_meshes(path, use_kd)
+    s = Scene()
+    has_n = m["normals"].size > 0
+    s.add_triangle_mesh(m["positions"], m["position_triplets"], m["normals"] if has_n else None,
+                        m["normal_triplets"] if has_n else None, m["material_id"], m["albedo"])
+    s.commit(device)
+    return s
 
 
 class Scene:
