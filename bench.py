@@ -198,12 +198,17 @@ def run_ours(args):
     if args.spp:
         spp = args.spp
     sd = gen()
+    N = W * H
     t0 = time.perf_counter()
     scene = wpt.scene_from(sd, device=local)
     commit_s = time.perf_counter() - t0
     bst = scene.stats()
     cam = wpt.camera_from(sd)
-    N = W * H
+    if args.spp_per_pass <= 0:
+        # paths in flight per pass: as many samples as fit 2^28 paths (96 B of queue each, 25 GB), at most
+        # 64 — measured on C3 (profiles/): 4 -> 3349, 8 -> 3564, 16 -> 3679, 32 -> 3746, 64 -> 3803 Mrays/s;
+        # late bounces hold few paths and a persistent-kernel launch has a fixed ramp-up/drain cost
+        args.spp_per_pass = int(max(1, min(spp, 64, (1 << 28) // N)))
     r = wpt.Renderer(scene, W, H, args.spp_per_pass)
     r.set_tuning(args.variant, args.ctas_per_sm, 0)
     film = torch.zeros(3, N, device="cuda")
@@ -321,7 +326,7 @@ def run_ours(args):
                 "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
                            "spp": spp, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
-                               N * args.spp_per_pass * 56 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
+                               N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
                                    "build_ms": bst["build_ms"], "upload_ms": bst["upload_ms"]}},
                 "ms_per_frame": ms / args.steps, "segments_per_step": segs_all / args.steps,
@@ -341,7 +346,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4", "C5"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp")
-    ap.add_argument("--spp-per-pass", type=int, default=4)
+    ap.add_argument("--spp-per-pass", type=int, default=0, help="samples in flight per pass (0 = auto)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")

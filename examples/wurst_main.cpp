@@ -1,0 +1,63 @@
+// wurst_main.cpp — the reference's main() (src/main.cpp:355-445) on libwpt.so through include/wpt_shim.hpp:
+// load an OBJ, commit, render num_samples x num_bounces with the reference's default thin-lens camera,
+// normalise, write wurst.pfm.  Same statement order; the per-sample / per-bounce loop body
+// (main.cpp:385-426) is the one call PathLoop::render.
+//
+//   wurst [scene.obj] [out.pfm] [width height num_samples num_bounces] [--kd]
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+
+#include "wpt_shim.hpp"
+
+using namespace wpt_shim;
+
+int main(int argc, char **argv)
+{
+    // all const (src/main.cpp:357-362)
+    const char *obj = argc > 1 ? argv[1] : "mitsuba.obj";
+    const char *out = argc > 2 ? argv[2] : "wurst.pfm";
+    const int width = argc > 3 ? std::atoi(argv[3]) : 512;
+    const int height = argc > 4 ? std::atoi(argv[4]) : 512;
+    const int num_samples = argc > 5 ? std::atoi(argv[5]) : 100;
+    const int num_bounces = argc > 6 ? std::atoi(argv[6]) : 2;
+    bool use_kd = false;
+    for (int i = 1; i < argc; i++) use_kd = use_kd || std::strcmp(argv[i], "--kd") == 0;
+    try {
+        // load meshes and materials (src/main.cpp:364-366)
+        Scene scene;
+        scene.add_triangle_mesh(obj, use_kd);
+        scene.commit();
+
+        // init film (src/main.cpp:369)
+        Film film(width, height);
+
+        // init timer (src/main.cpp:372-373)
+        StopWatch sw;
+        sw.reset();
+
+        // camera (src/main.cpp:383)
+        const float pi = 3.14159265358979323846f;
+        const ThinlensCamera thinlens(Real3(0.0f, 3.03f, 5.0f), Real3(0.0f, 0.03f, 0.0f), Real3(0.0f, 1.0f, 0.0f), 0.00f,
+                                      1.0f, 40.0f / 180.0f * pi);
+
+        // samples x bounces, film /= num_samples (src/main.cpp:385-429)
+        PathLoop loop(scene, width, height);
+        const wpt_stats st = loop.render(thinlens, num_samples, num_bounces, film);
+
+        std::cout << sw.timeMilliSec() << std::endl;    // src/main.cpp:431
+        std::cerr << st.segments << " ray segments, " << st.ms_total << " ms on the device, " << st.kernel_launches
+                  << " kernel launches" << std::endl;
+
+        // image write (src/main.cpp:433-442)
+        std::cout << "writing image" << std::endl;
+        Fimage::save_pfm(film.r.data(), film.g.data(), film.b.data(), width, height, out);
+        std::cout << "done" << std::endl;
+    } catch (const std::exception &e) {
+        std::cerr << e.what() << std::endl;
+        return 1;
+    }
+    return 0;
+}

@@ -442,10 +442,24 @@ void orc_shade_step(const orc_mesh *m, const float o[3], const float d[3], int32
                     float v, const float s[2], float next_o[3], float next_d[3], float weight[3])
 {
     for (int k = 0; k < 3; k++) next_o[k] = o[k] + t * d[k];
-    const float *n0 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 0];
-    const float *n1 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 1];
-    const float *n2 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 2];
-    float n[3], fr[9], local[3];
+    float n[3], fr[9], local[3], gn[3];
+    const float *n0 = gn, *n1 = gn, *n2 = gn;
+    if (m->nrm && m->nrm_idx && m->nrm_idx[3 * tri] >= 0 && m->nrm_idx[3 * tri + 1] >= 0 && m->nrm_idx[3 * tri + 2] >= 0) {
+        n0 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 0];
+        n1 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 1];
+        n2 = m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 2];
+    } else {
+        /* DOCUMENTED DEVIATION (include/wpt.h): a face without normals — where the reference
+         * gathers out of bounds (optix_backend.h:412-420 with index -1) — shades with its geometric normal,
+         * normalize(cross(p1-p0, p2-p0)) (add_math.h:9-16), at all three corners. */
+        const float *p0 = m->pos + 3 * (size_t)m->pos_idx[3 * tri], *p1 = m->pos + 3 * (size_t)m->pos_idx[3 * tri + 1],
+                    *p2 = m->pos + 3 * (size_t)m->pos_idx[3 * tri + 2];
+        const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] };
+        const float e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
+        gn[0] = e1[1] * e2[2] - e1[2] * e2[1]; gn[1] = e1[2] * e2[0] - e1[0] * e2[2]; gn[2] = e1[0] * e2[1] - e1[1] * e2[0];
+        const float l = sqrtf(gn[0] * gn[0] + gn[1] * gn[1] + gn[2] * gn[2]);
+        if (l > 0) { gn[0] /= l; gn[1] /= l; gn[2] /= l; } else { gn[0] = 0; gn[1] = 1; gn[2] = 0; }
+    }
     orc_barycentric3(n0, n1, n2, u, v, n);
     orc_frame_from_normal(n, fr);
     orc_cosine_hemisphere(s, local);

@@ -333,3 +333,62 @@ def test_errors(torch_cuda):
     s.add_triangle_mesh([[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 1, 5]])
     with pytest.raises(wpt.WptError):
         s.commit(0)           # index out of range is caught by the builder
+
+
+# ---------------------------------------------------------------- row f4: thin lens with lens_radius > 0
+def _lens_cameras(sd, radius, focal):
+    import wpt
+    c = sd.camera
+    cam = wpt.ThinlensCamera(c["look_from"], c["look_at"], c["up"], radius, focal, c["fov_y"])
+    ocam = util.oracle_camera(sd, lens_radius=radius, focal_dist=focal)
+    return cam, ocam
+
+
+def test_thin_lens_raygen_vs_oracle(torch_cuda):
+    """src/pinhole.h:27-32 with lens_radius > 0: Shirley disk (src/mapping.h:15-27) scaled by the radius,
+    placed in the camera's local x-z plane (sic), then sample_dir through the focal point (pinhole.h:34-56).
+    Every pixel of one sample against the oracle with the same Philox numbers."""
+    import ctypes as C
+    import wpt
+    sd = scenes.cornell(8)
+    cam, ocam = _lens_cameras(sd, 0.35, 2.5)
+    W, H = 40, 24
+    o_t, d_t = wpt.raygen(cam, W, H, 5, seed=4242)
+    o = np.stack([x.cpu().numpy() for x in o_t], 1)
+    d = np.stack([x.cpu().numpy() for x in d_t], 1)
+    L = O.lib()
+    on_lens = 0
+    for pix in range(W * H):
+        ctr = (C.c_uint32 * 4)(pix, 5, 0, 0)
+        key = (C.c_uint32 * 2)(4242, 0)
+        r = (C.c_uint32 * 4)()
+        L.orc_philox4x32_10(ctr, key, r)
+        xi = (C.c_float * 4)(*[L.orc_u32_to_f32(C.c_uint32(x)) for x in r])
+        po, pd = (C.c_float * 3)(), (C.c_float * 3)()
+        L.orc_camera_sample_pos(C.byref(ocam), xi, po)
+        xi2 = (C.c_float * 2)(xi[2], xi[3])
+        L.orc_camera_sample_dir(C.byref(ocam), C.c_int(pix % W), C.c_int(pix // W), po, C.c_int(W), C.c_int(H), xi2, pd)
+        assert np.abs(np.array(po) - o[pix]).max() <= 2e-6, pix        # sincos.approx vs libm: stated tolerance
+        assert np.abs(np.array(pd) - d[pix]).max() <= 4e-6, pix
+        on_lens += np.linalg.norm(o[pix] - np.float32(sd.camera["look_from"])) <= 0.35 * (1 + 1e-5)
+    assert on_lens == W * H
+    assert np.ptp(o[:, 0]) > 0.3                                       # the origins really spread over the lens
+
+
+def test_thin_lens_render_matches_oracle(torch_cuda):
+    """whole loop with depth of field: same-RNG image equal to the oracle's except at hit flips"""
+    import wpt
+    sd = scenes.cornell(24, colored=True)
+    cam, ocam = _lens_cameras(sd, 0.2, 3.0)
+    W = H = 96
+    scene = wpt.scene_from(sd)
+    film, st = wpt.Renderer(scene, W, H, 2).render_host(cam, 0, 4, 5, seed=9)
+    om = util.oracle_mesh(sd)
+    ofilm, oseg = om.render("bvh", ocam, W, H, 0, 4, 5, rng_mode=O.RNG_PHILOX, seed=9)
+    ofilm /= 4
+    diff = np.abs(film - ofilm).max(0)
+    assert (diff > 1e-5).mean() < 0.02, f"{(diff > 1e-5).mean()} of pixels differ"
+    assert abs(st["segments"] - oseg) <= 2e-3 * oseg
+    # and it is not the pinhole image
+    pin = wpt.Renderer(scene, W, H, 2).render_host(wpt.camera_from(sd), 0, 4, 5, seed=9)[0]
+    assert (np.abs(pin - film).max(0) > 1e-3).mean() > 0.2
