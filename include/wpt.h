@@ -68,6 +68,15 @@ int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
  * one upload to `device`. */
 int  wpt_scene_commit(wpt_scene *s, int device);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
+/* Moved vertices, same topology: bottom-up refit of the node boxes and rewrite of the triangle blocks ON THE
+ * DEVICE, one launch per tree level (the reference rebuilds its GAS from scratch,
+ * src/accel/optix_backend.h:283-364).  Hits stay exact — boxes are re-quantised conservatively — but tree
+ * quality decays with the deformation; commit again to rebuild.  Vertex normals are kept; faces that shade
+ * with the geometric normal get the new one.  wpt_scene_refit takes HOST positions f32[3*n_positions]
+ * (count must match; synchronous); wpt_scene_refit_device takes a DEVICE array and is asynchronous on
+ * `stream` (the host copy used by a later wpt_scene_commit is then NOT updated). */
+int  wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions);
+int  wpt_scene_refit_device(wpt_scene *s, const float *d_positions, void *stream);
 void wpt_scene_destroy(wpt_scene *s);
 
 /* ------------------------------------------------------------------ OBJ / MTL ingestion

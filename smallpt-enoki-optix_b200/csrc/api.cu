@@ -44,6 +44,13 @@ struct wpt_scene {
     TriAttr48 *d_attr = nullptr;
     float *d_albedo = nullptr;
     uint32_t *d_cursor = nullptr;   // scratch cursor for wpt_intersect
+    // refit (wpt_scene_refit): BFS levels of the node blocks, geometric-normal flags; vertex/index/box
+    // buffers are allocated by the first refit
+    uint32_t *d_level_nodes = nullptr;
+    uint8_t *d_geo = nullptr;
+    float *d_pos = nullptr, *d_boxes = nullptr;
+    int32_t *d_pidx = nullptr;
+    std::vector<uint32_t> level_begin;
     BvhView view{};
     wpt_bvh_stats stats{};
 };
@@ -84,8 +91,10 @@ static void scene_free_device(wpt_scene *s)
     if (s->device >= 0) cudaSetDevice(s->device);
     cudaFree(s->d_blocks); cudaFree(s->d_attr);
     cudaFree(s->d_albedo); cudaFree(s->d_cursor);
+    cudaFree(s->d_level_nodes); cudaFree(s->d_geo); cudaFree(s->d_pos); cudaFree(s->d_boxes); cudaFree(s->d_pidx);
     s->d_blocks = nullptr; s->d_attr = nullptr;
     s->d_albedo = nullptr; s->d_cursor = nullptr;
+    s->d_level_nodes = nullptr; s->d_geo = nullptr; s->d_pos = nullptr; s->d_boxes = nullptr; s->d_pidx = nullptr;
     s->committed = false;
 }
 
@@ -112,11 +121,13 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
 
     // per-ORIGINAL-triangle shading attributes: 3 vertex normals + material, one 48 B gather per hit
     std::vector<TriAttr48> attr(s->n_tris);
+    std::vector<uint8_t> geo(s->n_tris, 0);
     const bool has_n = !s->nidx.empty();
     for (uint32_t t = 0; t < s->n_tris; t++) {
         TriAttr48 &a = attr[t];
         bool ok = has_n;
         if (ok) for (int k = 0; k < 3; k++) ok = ok && s->nidx[3 * t + k] >= 0;
+        geo[t] = ok ? 0 : 1;
         if (ok) {
             for (int k = 0; k < 3; k++) {
                 a.n0[k] = s->nrm[3 * (size_t)s->nidx[3 * t + 0] + k];
@@ -151,6 +162,11 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMalloc(&s->d_level_nodes, b.level_nodes.size() * sizeof(uint32_t)));
+    WPT_CUDA(cudaMalloc(&s->d_geo, geo.size()));
+    WPT_CUDA(cudaMemcpy(s->d_level_nodes, b.level_nodes.data(), b.level_nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_geo, geo.data(), geo.size(), cudaMemcpyHostToDevice));
+    s->level_begin = b.level_begin;
     WPT_CUDA(cudaDeviceSynchronize());
     const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 
@@ -177,6 +193,45 @@ extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
     if (!s || !out) return fail(WPT_E_INVALID, "wpt_scene_stats: null argument");
     if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_stats: scene not committed");
     *out = s->stats;
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// refit for moved vertices (same topology): csrc/refit.cu
+static int refit_common(wpt_scene *s, const float *d_positions, cudaStream_t st)
+{
+    if (!s->d_boxes) {
+        WPT_CUDA(cudaMalloc(&s->d_boxes, (size_t)s->view.n_blocks * 6 * sizeof(float)));
+        WPT_CUDA(cudaMalloc(&s->d_pidx, s->pidx.size() * sizeof(int32_t)));
+        WPT_CUDA(cudaMemcpy(s->d_pidx, s->pidx.data(), s->pidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    launch_refit(s->d_blocks, s->d_level_nodes, s->level_begin.data(), (uint32_t)s->level_begin.size() - 1, d_positions,
+                 s->d_pidx, s->d_boxes, s->d_attr, s->d_geo, st);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+extern "C" int wpt_scene_refit_device(wpt_scene *s, const float *d_positions, void *stream)
+{
+    if (!s || !d_positions) return fail(WPT_E_INVALID, "wpt_scene_refit_device: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_refit_device: scene not committed");
+    WPT_CUDA(cudaSetDevice(s->device));
+    return refit_common(s, d_positions, (cudaStream_t)stream);
+}
+
+extern "C" int wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions)
+{
+    if (!s || !positions) return fail(WPT_E_INVALID, "wpt_scene_refit: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_refit: scene not committed");
+    if ((size_t)n_positions * 3 != s->pos.size()) return fail(WPT_E_INVALID, "wpt_scene_refit: vertex count differs from the committed mesh");
+    for (size_t k = 0; k < s->pos.size(); k++)
+        if (!std::isfinite(positions[k])) return fail(WPT_E_INVALID, "wpt_scene_refit: non-finite vertex");
+    WPT_CUDA(cudaSetDevice(s->device));
+    if (!s->d_pos) WPT_CUDA(cudaMalloc(&s->d_pos, s->pos.size() * sizeof(float)));
+    s->pos.assign(positions, positions + s->pos.size());
+    WPT_CUDA(cudaMemcpy(s->d_pos, positions, s->pos.size() * sizeof(float), cudaMemcpyHostToDevice));
+    if (int rc = refit_common(s, s->d_pos, nullptr)) return rc;
+    WPT_CUDA(cudaDeviceSynchronize());
     return WPT_OK;
 }
 

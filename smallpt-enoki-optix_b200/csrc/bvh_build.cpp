@@ -345,6 +345,8 @@ bool build_bvh7(const float *positions, uint32_t n_pos, const int32_t *triplets,
         const Work w = queue[qi];
         out.max_depth = std::max(out.max_depth, w.depth);
         out.n_nodes++;
+        while (out.level_begin.size() < w.depth) out.level_begin.push_back((uint32_t)out.level_nodes.size());
+        out.level_nodes.push_back(w.block);
         uint32_t kids[W];
         const int nk = col.gather_root(w.bvh2, kids);
         const Box nb = n2[w.bvh2].b;
@@ -443,6 +445,7 @@ bool build_bvh7(const float *positions, uint32_t n_pos, const int32_t *triplets,
         }
         out.blocks[w.block].node = node;
     }
+    out.level_begin.push_back((uint32_t)out.level_nodes.size());
     out.sah_cost = sah;
     if (out.max_depth > (uint32_t)kStackSize - 1) { *err = e_depth; return false; }
     out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

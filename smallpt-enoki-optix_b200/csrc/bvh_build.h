@@ -13,6 +13,9 @@ struct BuiltBvh {
     uint32_t max_depth = 0;        // wide-tree depth (root = 1)
     double   sah_cost = 0.0;
     double   build_ms = 0.0;
+    // node block indices in breadth-first order and, per depth d (root = 0), where that level starts
+    // (level_begin has max_depth + 1 entries): what a bottom-up refit sweeps, deepest level first
+    std::vector<uint32_t> level_nodes, level_begin;
 };
 
 // positions f32[3*n_pos], triplets i32[3*n_tris].  Returns false + message on invalid input

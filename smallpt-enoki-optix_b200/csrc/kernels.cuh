@@ -57,6 +57,9 @@ void launch_shade_streams(uint32_t n, const float *const o[3], const float *cons
                           const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
                           float *const w[3], cudaStream_t st);
 void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st);
+void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
+                  const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,
+                  cudaStream_t st);
 void launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, cudaStream_t st);
 
 }  // namespace wpt

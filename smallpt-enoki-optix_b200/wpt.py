@@ -78,6 +78,8 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.wpt_last_error.restype = C.c_char_p
         L.wpt_obj_free.argtypes = [C.c_void_p]
+        L.wpt_scene_refit.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.wpt_scene_refit_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.wpt_obj_mesh.argtypes = [C.c_void_p, C.c_void_p]
         L.wpt_obj_texcoords.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.wpt_obj_material_name.argtypes = [C.c_void_p, C.c_uint32]
@@ -220,6 +222,16 @@ class Scene:
             raise WptError(3, "Scene.commit: no mesh")
         _check(lib().wpt_scene_commit(self._h, C.c_int(device)))
         self.device = device
+
+    def refit(self, positions):
+        """wpt_scene_refit: moved vertices, same topology.  positions: host (V,3) float32, or a CUDA float32
+        tensor of 3V elements (device path, asynchronous on the current stream)."""
+        if isinstance(positions, np.ndarray) or isinstance(positions, (list, tuple)):
+            pos = _np(positions, np.float32).reshape(-1)
+            _check(lib().wpt_scene_refit(self._h, C.c_void_p(pos.ctypes.data), C.c_uint32(pos.size // 3)))
+        else:
+            assert positions.is_cuda and positions.is_contiguous()
+            _check(lib().wpt_scene_refit_device(self._h, C.c_void_p(positions.data_ptr()), _stream_handle(None)))
 
     def stats(self):
         s = BvhStats()
