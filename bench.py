@@ -210,7 +210,9 @@ def run_ours(args):
         # late bounces hold few paths and a persistent-kernel launch has a fixed ramp-up/drain cost
         args.spp_per_pass = int(max(1, min(spp, 64, (1 << 28) // N)))
     r = wpt.Renderer(scene, W, H, args.spp_per_pass)
-    r.set_tuning(args.variant, args.ctas_per_sm, 0)
+    # two lanes: each trace launch asks for 6 CTAs/SM (measured: 3 -> 3564, 4 -> 3817, 5 -> 3845, 6 -> 3862, 7 -> 3856;
+    # serial 7 CTAs/SM 3791 Mrays/s)
+    r.set_tuning(args.variant, args.ctas_per_sm or (6 if args.overlap else 0), args.overlap)
     film = torch.zeros(3, N, device="cuda")
     import wpt_dist as wdist
     spp_begin, _ = wdist.spp_range_weak(rank, world, spp)   # disjoint, decorrelated (RNG keyed on global index)
@@ -349,6 +351,7 @@ def main():
     ap.add_argument("--spp-per-pass", type=int, default=0, help="samples in flight per pass (0 = auto)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--overlap", type=int, default=1, help="1 = two lanes on two streams (shade of one overlaps trace of the other)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()

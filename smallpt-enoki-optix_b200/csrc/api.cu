@@ -418,6 +418,16 @@ struct wpt_renderer {
     PassCounters *counters = nullptr; // one per pass slot, zeroed per pass
     unsigned long long *live_acc = nullptr;   // [WPT_MAX_DEPTH]
     float *film = nullptr;            // 3*W*H, used by wpt_render_host only
+    // overlap mode (wpt_renderer_set_tuning, third knob): a second set of queues on its own stream; passes
+    // alternate between the two lanes so that the HBM-bound shade/raygen kernels of one overlap the
+    // issue-bound trace kernel of the other.  Each lane then holds half of spp_per_pass.
+    bool overlap = false;
+    RayQueue q1[2]{};
+    int4 *hits1 = nullptr;
+    PassCounters *counters1 = nullptr;
+    unsigned long long *live_acc1 = nullptr;
+    cudaStream_t lane_stream[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
     bool profile = false;
     TraceTuning tune{0, 0};
     // bookkeeping of the render in flight
@@ -426,7 +436,7 @@ struct wpt_renderer {
     std::vector<int> prof_kind;               // 0 raygen, 1 trace, 2 shade
     uint32_t passes = 0, launches = 0;
     int depth_in_flight = 0;
-    bool in_flight = false;
+    bool in_flight = false, two_lanes_in_flight = false;
 };
 
 extern "C" void wpt_renderer_destroy(wpt_renderer *r)
@@ -435,6 +445,13 @@ extern "C" void wpt_renderer_destroy(wpt_renderer *r)
     if (r->scene && r->scene->device >= 0) cudaSetDevice(r->scene->device);
     for (int k = 0; k < 2; k++) { cudaFree(r->q[k].a); cudaFree(r->q[k].b); cudaFree(r->q[k].c); }
     cudaFree(r->hits); cudaFree(r->counters); cudaFree(r->live_acc); cudaFree(r->film);
+    for (int k = 0; k < 2; k++) { cudaFree(r->q1[k].a); cudaFree(r->q1[k].b); cudaFree(r->q1[k].c); }
+    cudaFree(r->hits1); cudaFree(r->counters1); cudaFree(r->live_acc1);
+    for (int k = 0; k < 2; k++) {
+        if (r->lane_stream[k]) cudaStreamDestroy(r->lane_stream[k]);
+        if (r->ev_join[k]) cudaEventDestroy(r->ev_join[k]);
+    }
+    if (r->ev_fork) cudaEventDestroy(r->ev_fork);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
     if (r->ev_end) cudaEventDestroy(r->ev_end);
     for (cudaEvent_t e : r->prof_events) cudaEventDestroy(e);
@@ -486,9 +503,29 @@ extern "C" int wpt_renderer_set_profile(wpt_renderer *r, int profile)
 extern "C" int wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int sort_rays)
 {
     if (!r) return fail(WPT_E_INVALID, "null renderer");
-    (void)sort_rays;
+    if (r->in_flight) return fail(WPT_E_STATE, "wpt_renderer_set_tuning: render in flight");
     r->tune.variant = trace_variant;
     r->tune.ctas_per_sm = ctas_per_sm;
+    const bool want = sort_rays != 0;      // third knob: two overlapping lanes
+    if (want && !r->hits1) {
+        const uint64_t cap1 = (uint64_t)r->W * r->H * (uint64_t)((r->spp_per_pass + 1) / 2);
+        cudaError_t e = cudaSetDevice(r->scene->device);
+        for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+            e = cudaMalloc(&r->q1[k].a, cap1 * sizeof(float4));
+            if (e == cudaSuccess) e = cudaMalloc(&r->q1[k].b, cap1 * sizeof(float4));
+            if (e == cudaSuccess) e = cudaMalloc(&r->q1[k].c, cap1 * sizeof(float2));
+        }
+        if (e == cudaSuccess) e = cudaMalloc(&r->hits1, cap1 * sizeof(int4));
+        if (e == cudaSuccess) e = cudaMalloc(&r->counters1, sizeof(PassCounters));
+        if (e == cudaSuccess) e = cudaMalloc(&r->live_acc1, sizeof(unsigned long long) * WPT_MAX_DEPTH);
+        for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+            e = cudaStreamCreateWithFlags(&r->lane_stream[k], cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_join[k], cudaEventDisableTiming);
+        }
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming);
+        if (e != cudaSuccess) return fail(WPT_E_CUDA, std::string("wpt_renderer_set_tuning: ") + cudaGetErrorString(e));
+    }
+    r->overlap = want;
     return WPT_OK;
 }
 
@@ -534,30 +571,56 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     };
     WPT_CUDA(cudaEventRecord(r->ev_begin, st));
     const uint32_t N = (uint32_t)r->W * r->H;
-    for (int s0 = 0; s0 < cfg->spp_count; s0 += r->spp_per_pass) {
-        const int ns = std::min(r->spp_per_pass, cfg->spp_count - s0);
+    // overlap mode: two lanes on their own streams, forked from and joined back into `st`; each lane takes
+    // every other pass of half the samples and its trace launches use half the CTAs.  Per-kernel profiling
+    // needs serial kernels, so it runs single-lane.
+    const bool two = r->overlap && !r->profile && cfg->spp_count > 1;
+    const int lane_spp = two ? (r->spp_per_pass + 1) / 2 : r->spp_per_pass;
+    TraceTuning tune = r->tune;
+    if (two) {
+        if (tune.ctas_per_sm <= 0) tune.ctas_per_sm = 3;
+        WPT_CUDA(cudaMemsetAsync(r->live_acc1, 0, sizeof(unsigned long long) * WPT_MAX_DEPTH, st));
+        WPT_CUDA(cudaEventRecord(r->ev_fork, st));
+        for (int k = 0; k < 2; k++) WPT_CUDA(cudaStreamWaitEvent(r->lane_stream[k], r->ev_fork, 0));
+    }
+    int pass_idx = 0;
+    for (int s0 = 0; s0 < cfg->spp_count; s0 += lane_spp, pass_idx++) {
+        const int ns = std::min(lane_spp, cfg->spp_count - s0);
         const int spp_first = cfg->spp_begin + s0;
         const uint32_t n_max = N * (uint32_t)ns;
-        WPT_CUDA(cudaMemsetAsync(r->counters, 0, sizeof(PassCounters), st));
+        const int lane = two ? (pass_idx & 1) : 0;
+        cudaStream_t ls = two ? r->lane_stream[lane] : st;
+        RayQueue *q = lane ? r->q1 : r->q;
+        int4 *hits = lane ? r->hits1 : r->hits;
+        PassCounters *counters = lane ? r->counters1 : r->counters;
+        unsigned long long *live_acc = lane ? r->live_acc1 : r->live_acc;
+        WPT_CUDA(cudaMemsetAsync(counters, 0, sizeof(PassCounters), ls));
         WPT_CUDA(mark(0));
-        launch_raygen(*cam, r->W, r->H, spp_first, ns, cfg->seed, r->q[0], &r->counters->qcount[0], st);
+        launch_raygen(*cam, r->W, r->H, spp_first, ns, cfg->seed, q[0], &counters->qcount[0], ls);
         WPT_CUDA(done());
         r->launches++;
         for (int j = 0; j < cfg->depth; j++) {
-            const RayQueue &qin = r->q[j & 1], &qout = r->q[(j + 1) & 1];
+            const RayQueue &qin = q[j & 1], &qout = q[(j + 1) & 1];
             WPT_CUDA(mark(1));
-            launch_trace_queue(s->view, qin, r->hits, &r->counters->qcount[j], &r->counters->cursor[j],
-                               r->live_acc + j, cfg->tmin, cfg->tmax, n_max, s->num_sms, r->tune, st);
+            launch_trace_queue(s->view, qin, hits, &counters->qcount[j], &counters->cursor[j],
+                               live_acc + j, cfg->tmin, cfg->tmax, n_max, s->num_sms, tune, ls);
             WPT_CUDA(done());
             WPT_CUDA(mark(2));
-            launch_shade(qin, r->hits, &r->counters->qcount[j], qout, &r->counters->qcount[j + 1],
+            launch_shade(qin, hits, &counters->qcount[j], qout, &counters->qcount[j + 1],
                          reinterpret_cast<const float4 *>(s->d_attr), s->d_albedo, j, cfg->depth, spp_first,
-                         cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, st);
+                         cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, ls);
             WPT_CUDA(done());
             r->launches += 2;
         }
         r->passes++;
     }
+    if (two) {
+        for (int k = 0; k < 2; k++) {
+            WPT_CUDA(cudaEventRecord(r->ev_join[k], r->lane_stream[k]));
+            WPT_CUDA(cudaStreamWaitEvent(st, r->ev_join[k], 0));
+        }
+    }
+    r->two_lanes_in_flight = two;
     WPT_CUDA(cudaEventRecord(r->ev_end, st));
     WPT_CUDA(cudaGetLastError());
     r->in_flight = true;
@@ -577,6 +640,10 @@ extern "C" int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream
     unsigned long long live[WPT_MAX_DEPTH];
     WPT_CUDA(cudaMemcpy(live, r->live_acc, sizeof live, cudaMemcpyDeviceToHost));
     for (int j = 0; j < r->depth_in_flight; j++) { stats->live[j] = live[j]; stats->segments += live[j]; }
+    if (r->two_lanes_in_flight) {
+        WPT_CUDA(cudaMemcpy(live, r->live_acc1, sizeof live, cudaMemcpyDeviceToHost));
+        for (int j = 0; j < r->depth_in_flight; j++) { stats->live[j] += live[j]; stats->segments += live[j]; }
+    }
     stats->passes = r->passes;
     stats->kernel_launches = r->launches;
     WPT_CUDA(cudaEventElapsedTime(&stats->ms_total, r->ev_begin, r->ev_end));

@@ -392,3 +392,29 @@ def test_thin_lens_render_matches_oracle(torch_cuda):
     # and it is not the pinhole image
     pin = wpt.Renderer(scene, W, H, 2).render_host(wpt.camera_from(sd), 0, 4, 5, seed=9)[0]
     assert (np.abs(pin - film).max(0) > 1e-3).mean() > 0.2
+
+
+def test_overlap_lanes_render_the_same_frame(torch_cuda):
+    """wpt_renderer_set_tuning third knob: two lanes on two streams (every other pass each).  Same counters,
+    same paths: segment counts equal, film equal (sums of the same terms; atomics order only)."""
+    import torch
+    import wpt
+    sd = scenes.cornell(16, colored=True)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    W = H = 96
+    out = []
+    for overlap, per_pass in ((0, 4), (1, 4), (1, 3), (1, 16)):
+        r = wpt.Renderer(scene, W, H, per_pass)
+        r.set_tuning(0, 0, overlap)
+        f = torch.zeros(3, W * H, device="cuda")
+        for _ in range(2):                                   # twice: the lanes' buffers are reused
+            f.zero_()
+            r.render(cam, f, 3, 11, 5, seed=8)
+            st = r.finish()
+        out.append((f.clone(), st))
+        r.close()
+    for f, st in out[1:]:
+        assert st["segments"] == out[0][1]["segments"] and st["live"] == out[0][1]["live"]
+        assert torch.allclose(f, out[0][0], rtol=0, atol=1e-5)
+    assert out[1][1]["passes"] == 6 and out[0][1]["passes"] == 3
