@@ -290,6 +290,8 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
     roof = None
     if rank == 0:
+        # per-kernel events need serial kernels: single lane, the kernel's own occupancy (7 CTAs/SM)
+        r.set_tuning(args.variant, args.ctas_per_sm, 0)
         r.set_profile(True)
         film.zero_()
         r.render(cam, film, spp_begin, spp, depth, seed=SEED)

@@ -162,8 +162,11 @@ int  wpt_renderer_create(const wpt_scene *s, int32_t width, int32_t height, int3
                          wpt_renderer **out);
 void wpt_renderer_destroy(wpt_renderer *r);
 int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
-/* Tuning knobs (0 = default): which trace kernel, CTAs per SM, block size. */
-int  wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int sort_rays);
+/* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders
+ * alternate passes on two internal streams (each lane holds half of spp_per_pass in its own queues) so that
+ * the HBM-bound raygen/shade kernels of one lane overlap the issue-bound trace kernel of the other.  Same
+ * paths, same film up to fp32 atomic order.  Not allowed while a render is in flight (WPT_E_STATE). */
+int  wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int overlap_lanes);
 
 /* Adds the UN-normalised sum of the requested samples into DEVICE planar film_r/g/b
  * (pixel_index = y*W + x, src/main.cpp:379-381,407).  Asynchronous on `stream`; `stats` (optional,

@@ -500,13 +500,13 @@ extern "C" int wpt_renderer_set_profile(wpt_renderer *r, int profile)
     return WPT_OK;
 }
 
-extern "C" int wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int sort_rays)
+extern "C" int wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int overlap_lanes)
 {
     if (!r) return fail(WPT_E_INVALID, "null renderer");
     if (r->in_flight) return fail(WPT_E_STATE, "wpt_renderer_set_tuning: render in flight");
     r->tune.variant = trace_variant;
     r->tune.ctas_per_sm = ctas_per_sm;
-    const bool want = sort_rays != 0;      // third knob: two overlapping lanes
+    const bool want = overlap_lanes != 0;
     if (want && !r->hits1) {
         const uint64_t cap1 = (uint64_t)r->W * r->H * (uint64_t)((r->spp_per_pass + 1) / 2);
         cudaError_t e = cudaSetDevice(r->scene->device);

@@ -326,8 +326,8 @@ class Renderer:
     def set_profile(self, on):
         _check(lib().wpt_renderer_set_profile(self._h, C.c_int(1 if on else 0)))
 
-    def set_tuning(self, trace_variant=0, ctas_per_sm=0, sort_rays=0):
-        _check(lib().wpt_renderer_set_tuning(self._h, C.c_int(trace_variant), C.c_int(ctas_per_sm), C.c_int(sort_rays)))
+    def set_tuning(self, trace_variant=0, ctas_per_sm=0, overlap_lanes=0):
+        _check(lib().wpt_renderer_set_tuning(self._h, C.c_int(trace_variant), C.c_int(ctas_per_sm), C.c_int(overlap_lanes)))
 
     def _cfg(self, spp_begin, spp_count, depth, seed, tmin, tmax):
         return RenderConfig(self.width, self.height, spp_begin, spp_count, depth, seed, tmin, tmax)

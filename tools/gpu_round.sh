@@ -5,9 +5,9 @@ timeout 600 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; e
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/smoke.log
 timeout 900 python bench.py > gpurun_out/bench_full.log 2>&1; echo "bench exit $?" >> gpurun_out/bench_full.log
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2>&1
-timeout 300 python bench.py --quick --spp 4 --steps 1 --warmup 1 > gpurun_out/plain.log 2>&1 && \
+timeout 300 python bench.py --quick --overlap 0 --spp 4 --steps 1 --warmup 1 > gpurun_out/plain.log 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv \
-    python bench.py --quick --spp 4 --steps 1 --warmup 1 > gpurun_out/ncu_list.log 2>&1
+    python bench.py --quick --overlap 0 --spp 4 --steps 1 --warmup 1 > gpurun_out/ncu_list.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:trace_ -c 3 \
-    -f -o gpurun_out/${1:-trace_round} python bench.py --quick --spp 4 --steps 1 --warmup 1 > gpurun_out/ncu_full.log 2>&1
+    -f -o gpurun_out/${1:-trace_round} python bench.py --quick --overlap 0 --spp 4 --steps 1 --warmup 1 > gpurun_out/ncu_full.log 2>&1
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; tail -2 gpurun_out/bench_full.log | cut -c1-600
