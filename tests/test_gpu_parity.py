@@ -418,3 +418,18 @@ def test_overlap_lanes_render_the_same_frame(torch_cuda):
         assert st["segments"] == out[0][1]["segments"] and st["live"] == out[0][1]["live"]
         assert torch.allclose(f, out[0][0], rtol=0, atol=1e-5)
     assert out[1][1]["passes"] == 6 and out[0][1]["passes"] == 3
+
+
+def test_non_finite_rays_miss_and_terminate(torch_cuda, cornell):
+    """Embree's NaNTest / InfTest (tutorials/verify/verify.cpp:3051,3124) at this boundary: rays with a NaN or
+    infinite component come back as misses, the persistent kernel terminates, finite rays in the same launch
+    are untouched."""
+    from test_host_builder import _poison
+    sd, scene, om = cornell
+    o, d = util.random_rays(sd, 200_000, seed=31)
+    o2, d2, bad = _poison(o, d, seed=4)
+    base = _dev_intersect(torch_cuda, scene, o, d)
+    got = _dev_intersect(torch_cuda, scene, o2, d2)
+    assert bad.sum() > 10_000 and (got[0][bad] == -1).all()
+    for a, b in zip(base, got):
+        assert np.array_equal(a[~bad], b[~bad], equal_nan=True)

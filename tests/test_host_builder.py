@@ -98,3 +98,28 @@ def test_config_triangle_counts():
     assert np.isfinite(sd.pos).all() and np.abs(sd.pos).max() <= 10.0
     ln = np.linalg.norm(sd.nrm, axis=1)
     assert np.abs(ln - 1).max() < 1e-4
+
+
+def _poison(o, d, seed=0, frac=0.3):
+    """NaN / +-Inf in one component of the origin or direction of a random subset of the rays
+    (Embree's NaNTest / InfTest, dependencies/embree/tutorials/verify/verify.cpp:3051,3124)"""
+    rng = np.random.default_rng(seed)
+    o2, d2 = o.copy(), d.copy()
+    bad = rng.random(len(o)) < frac
+    vals = (np.nan, np.inf, -np.inf)
+    for i in np.nonzero(bad)[0]:
+        k = int(rng.integers(0, 6))
+        (o2 if k < 3 else d2)[i, k % 3] = vals[int(rng.integers(0, 3))]
+    return o2, d2, bad
+
+
+def test_non_finite_rays_miss_and_terminate(hosttest):
+    """a ray with a NaN or infinite component terminates, reports a miss, and leaves its neighbours alone"""
+    sd = scenes.cornell(12)
+    o, d = util.random_rays(sd, 20_000, seed=3)
+    base = util.hosttest_trace(hosttest, sd, o, d)
+    o2, d2, bad = _poison(o, d)
+    got = util.hosttest_trace(hosttest, sd, o2, d2)
+    assert bad.sum() > 1000 and (got[0][bad] == -1).all()
+    for a, b in zip(base, got):
+        assert np.array_equal(a[~bad], b[~bad], equal_nan=True)
