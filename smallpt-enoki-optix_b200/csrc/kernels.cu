@@ -184,8 +184,24 @@ struct WarpShared {
                                  // triangle block of the node, y = hit leaf slots << 16 | 2-bit triangle counts
 };
 
+// 256-bit block-half load with a selectable L1 hint.  Measured on C3 (profiles/r1_microbench.md): triangle blocks
+// are hardly ever re-used by the same SM, so they are loaded L1::no_allocate (+0.8 %); node loads must allocate —
+// the top three levels of the tree live in L1 (no_allocate on nodes: -20 %).
+template <int M>
+__device__ __forceinline__ void ld_half_m(const uint4 *p, uint4 &a, uint4 &b)
+{
+#define WPT_LD(S) asm(S " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p))
+    if (M == 0) WPT_LD("ld.global.nc.v8.b32");
+    if (M == 1) WPT_LD("ld.global.v8.b32");
+    if (M == 2) WPT_LD("ld.global.nc.L1::no_allocate.v8.b32");
+    if (M == 3) WPT_LD("ld.global.nc.L1::evict_last.v8.b32");
+    if (M == 4) WPT_LD("ld.global.nc.L1::evict_first.v8.b32");
+#undef WPT_LD
+}
+
 // every lane < k takes one queued entry (the leaves one node step hit, 1..3 triangles each), tests
 // them against the owner's ray and folds the closest accepted hit into the owner's record
+template <int LDT>
 __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, unsigned lane, uint32_t &qn, uint32_t k)
 {
     __syncwarp();
@@ -209,7 +225,7 @@ __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, 
             T ^= 1u << tb;
             const uint4 *tp = t0p + (size_t)tb * 4;
             uint4 ta, tb4, tc, td;
-            ld_block_half(tp, ta, tb4); ld_block_half(tp + 2, tc, td);
+            ld_half_m<LDT>(tp, ta, tb4); ld_half_m<LDT>(tp + 2, tc, td);
             if (tri_hit(as_f4(ta), as_f4(tb4), as_f4(tc), r, t, u, v)) { cand = true; prim = td.x; }
         }
         if (cand) atomicMin(&ws.hit_t[owner], __float_as_uint(t));
@@ -231,7 +247,7 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr)
     return v;
 }
 
-template <class IO, int FETCH_THRESHOLD, int MIN_CTAS, bool PACKED = false>
+template <class IO, int FETCH_THRESHOLD, int MIN_CTAS, bool PACKED = false, int LDN = 0, int LDT = 2>
 __global__ void __launch_bounds__(kTraceBlock, MIN_CTAS)
 trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
          uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
@@ -267,7 +283,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
         const unsigned act = __ballot_sync(0xffffffffu, state == 1);
         if (__popc(act) < (FETCH_THRESHOLD > 0 ? FETCH_THRESHOLD : 1)) {
             // drain the queue so that parked rays are final, store them, then refill
-            while (qn) flush_queue(bvh, ws, lane, qn, qn < 32u ? qn : 32u);
+            while (qn) flush_queue<LDT>(bvh, ws, lane, qn, qn < 32u ? qn : 32u);
             if (state == 2) {
                 io.store(ray_i, ws.hit_prim[lane], __uint_as_float(ws.hit_t[lane]), ws.hit_u[lane], ws.hit_v[lane]);
                 state = 0;
@@ -317,7 +333,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
             const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
             uint4 q0, q1, q2, q3;
-            ld_block_half(np, q0, q1); ld_block_half(np + 2, q2, q3);
+            ld_half_m<LDN>(np, q0, q1); ld_half_m<LDN>(np + 2, q2, q3);
             const uint32_t h7 = PACKED ? node_hits7_p(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]))
                                        : node_hits7(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
             const uint32_t imask = q2.w >> 24;
@@ -340,11 +356,11 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const bool has = L != 0u;
             const unsigned b = __ballot_sync(0xffffffffu, has);
             if (b) {
-                if (qn > (uint32_t)kQueueCap - 32u) flush_queue(bvh, ws, lane, qn, 32u);
+                if (qn > (uint32_t)kQueueCap - 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
                 if (has)
                     ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | cnt2);
                 qn += (uint32_t)__popc(b);
-                if (qn >= 32u) flush_queue(bvh, ws, lane, qn, 32u);
+                if (qn >= 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
             }
         }
     }
@@ -409,6 +425,7 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 8: launch(trace_wq<IO, 20, 6>); break;
     case 9: launch(trace_wq<IO, 20, 7, true>); break;
     case 10: launch(trace_wq<IO, 20, 6, true>); break;
+    case 11: launch(trace_wq<IO, 20, 7, false, 0, 0>); break;   // triangle loads allocate in L1 (the old default)
 
     default: launch(trace_wq<IO, 20, 7>); break;
     }
