@@ -210,9 +210,8 @@ def run_ours(args):
         # late bounces hold few paths and a persistent-kernel launch has a fixed ramp-up/drain cost
         args.spp_per_pass = int(max(1, min(spp, 64, (1 << 28) // N)))
     r = wpt.Renderer(scene, W, H, args.spp_per_pass)
-    # two lanes: each trace launch asks for 6 CTAs/SM (measured: 3 -> 3564, 4 -> 3817, 5 -> 3845, 6 -> 3862, 7 -> 3856;
-    # serial 7 CTAs/SM 3791 Mrays/s)
-    r.set_tuning(args.variant, args.ctas_per_sm or (6 if args.overlap else 0), args.overlap)
+    # two lanes (profiles/r1_microbench.md): every trace launch at the kernel's own occupancy (8 CTAs/SM, 64 registers)
+    r.set_tuning(args.variant, args.ctas_per_sm, args.overlap)
     film = torch.zeros(3, N, device="cuda")
     import wpt_dist as wdist
     spp_begin, _ = wdist.spp_range_weak(rank, world, spp)   # disjoint, decorrelated (RNG keyed on global index)
@@ -290,7 +289,7 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
     roof = None
     if rank == 0:
-        # per-kernel events need serial kernels: single lane, the kernel's own occupancy (7 CTAs/SM)
+        # per-kernel events need serial kernels: single lane, the kernel's own occupancy (8 CTAs/SM)
         r.set_tuning(args.variant, args.ctas_per_sm, 0)
         r.set_profile(True)
         film.zero_()

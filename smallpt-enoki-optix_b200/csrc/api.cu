@@ -572,13 +572,12 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     WPT_CUDA(cudaEventRecord(r->ev_begin, st));
     const uint32_t N = (uint32_t)r->W * r->H;
     // overlap mode: two lanes on their own streams, forked from and joined back into `st`; each lane takes
-    // every other pass of half the samples and its trace launches use half the CTAs.  Per-kernel profiling
+    // every other pass of half the samples.  Per-kernel profiling
     // needs serial kernels, so it runs single-lane.
     const bool two = r->overlap && !r->profile && cfg->spp_count > 1;
     const int lane_spp = two ? (r->spp_per_pass + 1) / 2 : r->spp_per_pass;
     TraceTuning tune = r->tune;
     if (two) {
-        if (tune.ctas_per_sm <= 0) tune.ctas_per_sm = 3;
         WPT_CUDA(cudaMemsetAsync(r->live_acc1, 0, sizeof(unsigned long long) * WPT_MAX_DEPTH, st));
         WPT_CUDA(cudaEventRecord(r->ev_fork, st));
         for (int k = 0; k < 2; k++) WPT_CUDA(cudaStreamWaitEvent(r->lane_stream[k], r->ev_fork, 0));

@@ -427,7 +427,7 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 10: launch(trace_wq<IO, 20, 6, true>); break;
     case 11: launch(trace_wq<IO, 20, 7, false, 0, 0>); break;   // triangle loads allocate in L1 (the old default)
 
-    default: launch(trace_wq<IO, 20, 7>); break;
+    default: launch(trace_wq<IO, 20, 8>); break;   // 64 registers, 8 CTAs (32 warps) per SM
     }
 }
 
