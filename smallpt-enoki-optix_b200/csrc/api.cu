@@ -1,6 +1,7 @@
 // api.cu — the C ABI of libwpt.so (include/wpt.h).  Host C++; owns device memory, never throws.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -43,7 +44,10 @@ struct wpt_scene {
     Block64 *d_blocks = nullptr;   // nodes and triangles, bvh.h
     TriAttr48 *d_attr = nullptr;
     float *d_albedo = nullptr;
-    uint32_t *d_cursor = nullptr;   // scratch cursor for wpt_intersect
+    // ray-fetch cursors of wpt_intersect: a ring of 64, one per call, so that calls on different streams
+    // (the BVH is read-only) do not share a counter
+    uint32_t *d_cursor = nullptr;
+    mutable std::atomic<uint32_t> cursor_rr{0};
     // refit (wpt_scene_refit): BFS levels of the node blocks, geometric-normal flags; vertex/index/box
     // buffers are allocated by the first refit
     uint32_t *d_level_nodes = nullptr;
@@ -321,8 +325,9 @@ extern "C" int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, co
     io.tmin = rays->tmin; io.tmax = rays->tmax; io.tmin_s = rays->tmin_scalar; io.tmax_s = rays->tmax_scalar;
     io.mask = mask; io.mask_size = mask_size;
     io.tri_id = hits->tri_id; io.t = hits->t; io.u = hits->u; io.v = hits->v;
-    WPT_CUDA(cudaMemsetAsync(s->d_cursor, 0, sizeof(uint32_t), st));
-    launch_trace_streams(s->view, io, n, s->d_cursor, s->num_sms, g_default_tune, st);
+    uint32_t *cursor = s->d_cursor + (s->cursor_rr.fetch_add(1u, std::memory_order_relaxed) & 63u);
+    WPT_CUDA(cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st));
+    launch_trace_streams(s->view, io, n, cursor, s->num_sms, g_default_tune, st);
     WPT_CUDA(cudaGetLastError());
     return WPT_OK;
 }
