@@ -178,6 +178,7 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     s->view.n_blocks = (uint32_t)b.blocks.size();
     s->view.n_nodes = b.n_nodes;
     s->view.n_tris = b.n_tris;
+    s->view.max_depth = b.max_depth;
     s->stats.n_triangles = s->n_tris;
     s->stats.n_nodes = b.n_nodes;
     s->stats.n_leaf_slots = b.n_tris;

@@ -64,6 +64,7 @@ static_assert(sizeof(TriAttr48) == 48, "TriAttr48 must be 48 bytes");
 struct BvhView {
     const uint4 *blocks;    // Block64 as 4 x uint4; block 0 is the root node
     uint32_t n_blocks, n_nodes, n_tris;
+    uint32_t max_depth;     // node levels, root = 1: a traversal stack needs at most max_depth - 1 entries
 };
 
 }  // namespace wpt

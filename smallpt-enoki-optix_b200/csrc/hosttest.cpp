@@ -93,7 +93,14 @@ int wpt_hosttest_build(const float *pos, uint32_t n_pos, const int32_t *idx, uin
     return 0;
 }
 
-// counters (optional): [0] node visits, [1] triangle tests, summed over all rays
+// LocalStack that remembers its high-water mark (the shared-memory-only trace kernels rely on
+// "a traversal never holds more than max_depth - 1 entries")
+struct CountingStack : LocalStack {
+    int hi = 0;
+    void push(uint2 v) { LocalStack::push(v); if (n > hi) hi = n; }
+};
+
+// counters (optional): [0] node visits, [1] triangle tests, summed over all rays; [2] deepest stack, [3] max_depth
 int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
                              const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
                              const float *dz, float tmin, float tmax, uint32_t n,
@@ -107,18 +114,21 @@ int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *id
     view.n_blocks = (uint32_t)b.blocks.size();
     view.n_nodes = b.n_nodes;
     view.n_tris = b.n_tris;
+    view.max_depth = b.max_depth;
     uint64_t nodes_visited = 0, tris_tested = 0;
-#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : nodes_visited, tris_tested)
+    int stack_hi = 0;
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : nodes_visited, tris_tested) reduction(max : stack_hi)
     for (int64_t i = 0; i < (int64_t)n; i++) {
         const RayCtx r = make_ray(ox[i], oy[i], oz[i], dx[i], dy[i], dz[i], tmin);
-        LocalStack st;
+        CountingStack st;
         uint64_t c[2] = {0, 0};
         const Hit h = trace_ray(view, r, tmax, st, c);
         nodes_visited += c[0]; tris_tested += c[1];
+        if (st.hi > stack_hi) stack_hi = st.hi;
         id[i] = h.prim;
         if (h.prim >= 0) { t[i] = h.t; u[i] = h.u; v[i] = h.v; }
     }
-    if (counters) { counters[0] = (double)nodes_visited; counters[1] = (double)tris_tested; }
+    if (counters) { counters[0] = (double)nodes_visited; counters[1] = (double)tris_tested; counters[2] = stack_hi; counters[3] = b.max_depth; }
     return 0;
 }
 

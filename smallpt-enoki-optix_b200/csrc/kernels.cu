@@ -236,6 +236,12 @@ __device__ __forceinline__ void flush_queue(const BvhView &bvh, WarpShared &ws, 
     qn -= k;
 }
 
+__device__ __forceinline__ uint32_t bfind_u32(uint32_t x)   // index of the highest set bit (FLO.U32)
+{
+    uint32_t r;
+    asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+    return r;
+}
 __device__ __forceinline__ void sts64(uint32_t addr, uint2 v)
 {
     asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
@@ -247,12 +253,12 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr)
     return v;
 }
 
-template <class IO, int FETCH_THRESHOLD, int MIN_CTAS, bool PACKED = false, int LDN = 0, int LDT = 2>
+template <class IO, int FETCH_THRESHOLD, int MIN_CTAS, bool PACKED = false, int LDN = 0, int LDT = 2, bool DEEP = true, int SST = kSmemStack>
 __global__ void __launch_bounds__(kTraceBlock, MIN_CTAS)
 trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uint32_t n_static,
          uint32_t *__restrict__ cursor, unsigned long long *__restrict__ live_acc)
 {
-    __shared__ uint2 sstack[kSmemStack * kTraceBlock];
+    __shared__ uint2 sstack[SST * kTraceBlock];
     __shared__ uint8_t perm_lut[8 * 128];
     __shared__ WarpShared wsh[kTraceBlock / 32];
     for (uint32_t i = threadIdx.x; i < 8u * 128u; i += kTraceBlock) perm_lut[i] = (uint8_t)perm8(i & 127u, i >> 7);
@@ -262,12 +268,13 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
     const unsigned lane = threadIdx.x & 31u;
     WarpShared &ws = wsh[threadIdx.x >> 5];
     // traversal stack: a shared-memory byte address that moves by one row (kTraceBlock entries) per
-    // push / pop; entries beyond kSmemStack spill to local memory (deep trees only)
+    // push / pop.  DEEP: entries beyond kSmemStack spill to local memory; the launcher picks the
+    // non-DEEP instantiation (no overflow code at all) when max_depth - 1 <= SST
     constexpr uint32_t kRow = kTraceBlock * (uint32_t)sizeof(uint2);
     const uint32_t s_base = (uint32_t)__cvta_generic_to_shared(sstack + threadIdx.x);
-    const uint32_t s_limit = s_base + kSmemStack * kRow;
+    const uint32_t s_limit = s_base + SST * kRow;
     uint32_t s_top = s_base;
-    uint2 lstack[kStackSize - kSmemStack];
+    uint2 lstack[DEEP ? kStackSize - SST : 1];
 
     // state: 0 = idle, 1 = traversing, 2 = parked (stack empty, waiting for the queue to drain)
     int state = 0;
@@ -320,16 +327,16 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                 break;
             }
         }
-        uint32_t L = 0, tri0 = 0, cnt2 = 0;   // hit leaf slots of this step
+        uint32_t L = 0, tri0, cnt2;   // hit leaf slots of this step (tri0, cnt2 are defined where L != 0)
         if (state == 1) {
-            // next internal child, front to back: highest pending priority bit
-            const int bit = 31 - __clz((int)G.y);
+            // next internal child, front to back: highest pending priority bit (24..31)
+            const uint32_t bit = bfind_u32(G.y);
             G.y ^= 1u << bit;
             if (G.y >> 24) {
-                if (s_top < s_limit) sts64(s_top, G); else lstack[(s_top - s_limit) / kRow] = G;
+                if (!DEEP || s_top < s_limit) sts64(s_top, G); else lstack[(s_top - s_limit) / kRow] = G;
                 s_top += kRow;
             }
-            const uint32_t slot = ((uint32_t)bit - 24u) ^ r.oct_inv;
+            const uint32_t slot = (bit ^ r.oct_inv) & 7u;       // = (bit - 24) ^ oct_inv
             const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
             const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
             uint4 q0, q1, q2, q3;
@@ -347,7 +354,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                     state = 2;
                 } else {
                     s_top -= kRow;
-                    G = s_top < s_limit ? lds64(s_top) : lstack[(s_top - s_limit) / kRow];
+                    G = (!DEEP || s_top < s_limit) ? lds64(s_top) : lstack[(s_top - s_limit) / kRow];
                 }
             }
         }
@@ -427,7 +434,12 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 10: launch(trace_wq<IO, 20, 6, true>); break;
     case 11: launch(trace_wq<IO, 20, 7, false, 0, 0>); break;   // triangle loads allocate in L1 (the old default)
 
-    default: launch(trace_wq<IO, 20, 8>); break;   // 64 registers, 8 CTAs (32 warps) per SM
+    default:   // 64 registers, 8 CTAs (32 warps) per SM; the stack lives in shared memory whenever the tree allows
+        // (a traversal needs at most max_depth - 1 entries: C1/C2 8 levels, C3 11, C4 13)
+        if (bvh.max_depth <= 11u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 10>);
+        else if (bvh.max_depth <= 15u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 14>);
+        else launch(trace_wq<IO, 20, 8>);
+        break;
     }
 }
 

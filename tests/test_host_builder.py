@@ -123,3 +123,23 @@ def test_non_finite_rays_miss_and_terminate(hosttest):
     assert bad.sum() > 1000 and (got[0][bad] == -1).all()
     for a, b in zip(base, got):
         assert np.array_equal(a[~bad], b[~bad], equal_nan=True)
+
+
+def test_stack_never_exceeds_tree_depth_minus_one(hosttest):
+    """the shared-memory-only trace kernels (csrc/kernels.cu, launch_trace_any) size the traversal stack from
+    max_depth: a traversal holds at most max_depth - 1 groups (the deepest nodes have no internal children)"""
+    import ctypes as C
+    for sd in (scenes.cornell(20), scenes.knob(120, 50), scenes.interior(33, 2, (16, 32))):
+        o, d = util.random_rays(sd, 200_000, seed=9)
+        n = o.shape[0]
+        cols = [np.ascontiguousarray(o[:, k]) for k in range(3)] + [np.ascontiguousarray(d[:, k]) for k in range(3)]
+        hid = np.full(n, -2, np.int32); t = np.full(n, np.nan, np.float32); u = t.copy(); v = t.copy()
+        cnt = (C.c_double * 4)()
+        rc = hosttest.wpt_hosttest_trace_stats(
+            sd.pos.ctypes.data_as(C.c_void_p), C.c_uint32(sd.pos.shape[0]), sd.idx.ctypes.data_as(C.c_void_p),
+            C.c_uint32(sd.n_tris), *[c.ctypes.data_as(C.c_void_p) for c in cols], C.c_float(1e-3), C.c_float(1e20),
+            C.c_uint32(n), hid.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p),
+            u.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p), cnt)
+        assert rc == 0
+        stack_hi, max_depth = int(cnt[2]), int(cnt[3])
+        assert max_depth >= 3 and 1 <= stack_hi <= max_depth - 1, (stack_hi, max_depth)

@@ -12,7 +12,7 @@ def stats(H, sd, o, d):
     n = o.shape[0]
     cols = [np.ascontiguousarray(o[:, k]) for k in range(3)] + [np.ascontiguousarray(d[:, k]) for k in range(3)]
     hid = np.full(n, -2, np.int32); t = np.full(n, np.nan, np.float32); u = t.copy(); v = t.copy()
-    cnt = (C.c_double * 2)()
+    cnt = (C.c_double * 4)()
     rc = H.wpt_hosttest_trace_stats(sd.pos.ctypes.data_as(C.c_void_p), C.c_uint32(sd.pos.shape[0]),
         sd.idx.ctypes.data_as(C.c_void_p), C.c_uint32(sd.n_tris), *[c.ctypes.data_as(C.c_void_p) for c in cols],
         C.c_float(1e-3), C.c_float(1e20), C.c_uint32(n), hid.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p),
