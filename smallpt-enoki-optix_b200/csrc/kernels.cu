@@ -341,13 +341,14 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
             uint4 q0, q1, q2, q3;
             ld_half_m<LDN>(np, q0, q1); ld_half_m<LDN>(np + 2, q2, q3);
+            // bits 0..6 = hit mask; the bits above are masked off by imask (<= 0x7f) / the 0x7f below
             const uint32_t h7 = PACKED ? node_hits7_p(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]))
-                                       : node_hits7(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
+                                       : node_hits7_raw(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
             const uint32_t imask = q2.w >> 24;
             G.x = q0.w;
             G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
-            L = h7 & ~imask;
-            cnt2 = (q3.y >> 24) | ((q3.w >> 24) << 8);
+            L = h7 & ~imask & 0x7fu;
+            cnt2 = __byte_perm(q3.y, q3.w, 0x3373);   // low half = the 2-bit triangle counts, high half unused
             tri0 = q0.w + (uint32_t)__popc(imask);
             if (!(G.y >> 24)) {
                 if (s_top == s_base) {
@@ -365,7 +366,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             if (b) {
                 if (qn > (uint32_t)kQueueCap - 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
                 if (has)
-                    ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | cnt2);
+                    ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | (cnt2 & 0xffffu));
                 qn += (uint32_t)__popc(b);
                 if (qn >= 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
             }

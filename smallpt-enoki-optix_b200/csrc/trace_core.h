@@ -115,8 +115,9 @@ WPT_HD RayCtx make_ray(float ox, float oy, float oz, float dx, float dy, float d
 // q3 for z.  Byte 7 of each array is header: xlo e[0]+8, xhi e[1]+8, ylo e[2]+8, yhi imask,
 // zlo / zhi triangle counts.  Returns the 7-bit mask of children (slot order) whose box the ray
 // segment [tmin, tmax] touches (empty slots hold an inverted box and never hit).
-WPT_HD uint32_t node_hits7(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3, const RayCtx &r,
-                           float tmax)
+// node_hits7_raw: the same mask in bits 0..6 of the float bits of 2^23 + mask (bits 7..31 are not zero)
+WPT_HD uint32_t node_hits7_raw(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3, const RayCtx &r,
+                               float tmax)
 {
     const float ax = u2f((q1.y >> 24) << 23) * r.ix;     // 256 * scale / d
     const float ay = u2f((q1.w >> 24) << 23) * r.iy;
@@ -140,7 +141,12 @@ WPT_HD uint32_t node_hits7(const uint4 q0, const uint4 q1, const uint4 q2, const
     }
     WPT_CHILD(0, 0) WPT_CHILD(0, 1) WPT_CHILD(0, 2) WPT_CHILD(0, 3) WPT_CHILD(1, 0) WPT_CHILD(1, 1) WPT_CHILD(1, 2)
 #undef WPT_CHILD
-    return f2u(acc) & 0x7fu;
+    return f2u(acc);
+}
+WPT_HD uint32_t node_hits7(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3, const RayCtx &r,
+                           float tmax)
+{
+    return node_hits7_raw(q0, q1, q2, q3, r, tmax) & 0x7fu;
 }
 
 #if defined(__CUDACC__)
