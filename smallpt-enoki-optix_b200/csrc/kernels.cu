@@ -364,7 +364,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const bool has = L != 0u;
             const unsigned b = __ballot_sync(0xffffffffu, has);
             if (b) {
-                if (qn > (uint32_t)kQueueCap - 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
+                // qn < 32 here (every iteration ends with qn < 32), so at most 63 entries are ever queued
                 if (has)
                     ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | (cnt2 & 0xffffu));
                 qn += (uint32_t)__popc(b);
