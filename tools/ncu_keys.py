@@ -26,4 +26,4 @@ keys = ["gpu__time_duration.sum", "smsp__issue_active.avg.pct_of_peak_sustained_
 for k in keys:
     if k in hdr:
         i = hdr.index(k)
-        print(f"{k:90s} {units[i]:8s}", [r[i][:10] for r in data])
+        print(f"{k:90s} {units[i]:8s}", [r[i][:14] for r in data])
