@@ -283,6 +283,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
     const uint8_t *lut = perm_lut;
     RayCtx r;
     uint2 G;
+    float tmax_r = 0.0f;   // this lane's closest t so far: changes only inside flush_queue, re-read after every flush
     G.x = G.y = 0u;
     r = make_ray(0.f, 0.f, 0.f, 0.f, 0.f, 1.f, 0.f);
 
@@ -290,7 +291,10 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
         const unsigned act = __ballot_sync(0xffffffffu, state == 1);
         if (__popc(act) < (FETCH_THRESHOLD > 0 ? FETCH_THRESHOLD : 1)) {
             // drain the queue so that parked rays are final, store them, then refill
-            while (qn) flush_queue<LDT>(bvh, ws, lane, qn, qn < 32u ? qn : 32u);
+            if (qn) {
+                do flush_queue<LDT>(bvh, ws, lane, qn, qn < 32u ? qn : 32u); while (qn);
+                tmax_r = __uint_as_float(ws.hit_t[lane]);
+            }
             if (state == 2) {
                 io.store(ray_i, ws.hit_prim[lane], __uint_as_float(ws.hit_t[lane]), ws.hit_u[lane], ws.hit_v[lane]);
                 state = 0;
@@ -312,6 +316,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                         ws.ray_a[lane] = make_float4(ox, oy, oz, dx);
                         ws.ray_b[lane] = make_float4(dy, dz, t0, 0.0f);
                         ws.hit_t[lane] = __float_as_uint(t1);
+                        tmax_r = t1;
                         ws.hit_prim[lane] = -1;
                         G.x = 0u; G.y = 0x01000000u;
                         s_top = s_base;
@@ -342,8 +347,8 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             uint4 q0, q1, q2, q3;
             ld_half_m<LDN>(np, q0, q1); ld_half_m<LDN>(np + 2, q2, q3);
             // bits 0..6 = hit mask; the bits above are masked off by imask (<= 0x7f) / the 0x7f below
-            const uint32_t h7 = PACKED ? node_hits7_p(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]))
-                                       : node_hits7_raw(q0, q1, q2, q3, r, __uint_as_float(ws.hit_t[lane]));
+            const uint32_t h7 = PACKED ? node_hits7_p(q0, q1, q2, q3, r, tmax_r)
+                                       : node_hits7_raw(q0, q1, q2, q3, r, tmax_r);
             const uint32_t imask = q2.w >> 24;
             G.x = q0.w;
             G.y = ((uint32_t)lut[h7 & imask] << 24) | imask;
@@ -368,7 +373,10 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                 if (has)
                     ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | (cnt2 & 0xffffu));
                 qn += (uint32_t)__popc(b);
-                if (qn >= 32u) flush_queue<LDT>(bvh, ws, lane, qn, 32u);
+                if (qn >= 32u) {
+                    flush_queue<LDT>(bvh, ws, lane, qn, 32u);
+                    tmax_r = __uint_as_float(ws.hit_t[lane]);
+                }
             }
         }
     }
