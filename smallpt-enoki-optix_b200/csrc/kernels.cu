@@ -442,6 +442,7 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 9: launch(trace_wq<IO, 20, 7, true>); break;
     case 10: launch(trace_wq<IO, 20, 6, true>); break;
     case 11: launch(trace_wq<IO, 20, 7, false, 0, 0>); break;   // triangle loads allocate in L1 (the old default)
+    case 12: launch(trace_wq<IO, 20, 8, false, 0, 2, true, 2>); break;   // test variant: two shared-memory stack rows, the rest overflows to local memory
 
     default:   // 64 registers, 8 CTAs (32 warps) per SM; the stack lives in shared memory whenever the tree allows
         // (a traversal needs at most max_depth - 1 entries: C1/C2 8 levels, C3 11, C4 13)

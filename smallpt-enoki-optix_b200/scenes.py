@@ -262,6 +262,17 @@ def interior(grid=289, n_pillars=8, pillar_grid=(64, 128), skylight=True, grey=0
     return b.finish("interior", albedo, cam)
 
 
+def spiral(n=80, q=0.75, n_phi=8):
+    """test scene with a DEEP tree: n small spheres in a geometric progression of size and position towards the
+    origin (the SAH peels one off per split): spiral(80, 0.75) -> 17 920 triangles, 17 node levels; (60, 0.7) -> 13"""
+    b = _Builder()
+    for i in range(n):
+        s = q ** i
+        b.add(*sphere([4.0 * s, 0.3 * s, 0.0], 0.15 * s, n_phi), mat=0)
+    cam = dict(look_from=(0.0, 0.0, 6.0), look_at=(1.0, 0.0, 0.0), up=(0, 1, 0), fov_y=40.0)
+    return b.finish("spiral", [[1, 1, 1]], cam)
+
+
 CONFIGS = {
     # name: (generator, W, H, spp, depth)   — BASELINE.json configs[0..4]
     "C1": (lambda: cornell(50), 256, 256, 4, 5),

@@ -278,7 +278,7 @@ def test_trace_variants_agree(torch_cuda):
     cam = wpt.camera_from(sd)
     W = H = 64
     films = []
-    for variant in (0, 1, 2, 5):
+    for variant in (0, 1, 2, 5, 12):   # 12: two shared stack rows, local-memory overflow exercised
         r = wpt.Renderer(scene, W, H, 2)
         r.set_tuning(trace_variant=variant)
         f = torch.zeros(3, W * H, device="cuda")
@@ -460,3 +460,19 @@ def test_intersect_concurrent_streams(torch_cuda, cornell):
             assert torch.equal(a[0] >= 0, b[0] >= 0)
             hit = a[0] >= 0
             assert torch.equal(a[1][hit], b[1][hit])
+
+
+def test_deep_trees_all_stack_variants(torch_cuda):
+    """the launcher sizes the shared-memory stack from the tree depth (10 rows up to 11 levels, 14 up to 15, local
+    memory overflow beyond): scenes.spiral gives 13 and 17 levels; hits must equal the oracle's either way"""
+    import wpt
+    from test_host_builder import _spiral_rays
+    for n, q, min_depth in ((60, 0.7, 12), (80, 0.75, 16)):
+        sd = scenes.spiral(n, q)
+        scene, om = wpt.scene_from(sd), util.oracle_mesh(sd)
+        assert scene.stats()["max_depth"] > min_depth
+        o, d = _spiral_rays(300_000, seed=n)
+        got = _dev_intersect(torch_cuda, scene, o, d)
+        ref = om.intersect("bvh", o, d)
+        assert (ref[0] >= 0).mean() > 0.2
+        assert util.compare_hits(ref, got, f"spiral {n}") >= 0.9999

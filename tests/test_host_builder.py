@@ -125,12 +125,25 @@ def test_non_finite_rays_miss_and_terminate(hosttest):
         assert np.array_equal(a[~bad], b[~bad], equal_nan=True)
 
 
+def _spiral_rays(n, seed=12):
+    """rays from around the large end of scenes.spiral towards points near its small end"""
+    rng = np.random.default_rng(seed)
+    o = np.stack([rng.uniform(3.0, 5.0, n), rng.uniform(-0.5, 1.0, n), rng.uniform(-1.0, 1.0, n)], 1)
+    s = 0.75 ** rng.uniform(0, 22, n)   # spheres down to 2e-3: below that fp32 hits are noise for any intersector
+    tgt = np.stack([4.0 * s, 0.3 * s, np.zeros(n)], 1) + rng.normal(size=(n, 3)) * (0.1 * s)[:, None]
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return o.astype(np.float32), d.astype(np.float32)
+
+
 def test_stack_never_exceeds_tree_depth_minus_one(hosttest):
     """the shared-memory-only trace kernels (csrc/kernels.cu, launch_trace_any) size the traversal stack from
     max_depth: a traversal holds at most max_depth - 1 groups (the deepest nodes have no internal children)"""
     import ctypes as C
-    for sd in (scenes.cornell(20), scenes.knob(120, 50), scenes.interior(33, 2, (16, 32))):
+    for sd in (scenes.cornell(20), scenes.knob(120, 50), scenes.interior(33, 2, (16, 32)), scenes.spiral(80, 0.75)):
         o, d = util.random_rays(sd, 200_000, seed=9)
+        if sd.name == "spiral":   # aim down the chain of ever smaller spheres
+            o, d = _spiral_rays(200_000)
         n = o.shape[0]
         cols = [np.ascontiguousarray(o[:, k]) for k in range(3)] + [np.ascontiguousarray(d[:, k]) for k in range(3)]
         hid = np.full(n, -2, np.int32); t = np.full(n, np.nan, np.float32); u = t.copy(); v = t.copy()
@@ -143,3 +156,5 @@ def test_stack_never_exceeds_tree_depth_minus_one(hosttest):
         assert rc == 0
         stack_hi, max_depth = int(cnt[2]), int(cnt[3])
         assert max_depth >= 3 and 1 <= stack_hi <= max_depth - 1, (stack_hi, max_depth)
+        if sd.name == "spiral":   # 17 levels: the launcher takes the kernel with the local-memory overflow
+            assert max_depth > 15 and stack_hi >= 5, (stack_hi, max_depth)
