@@ -197,6 +197,16 @@ def run_ours(args):
     gen, W, H, spp, depth = workload(args.workload)
     if args.spp:
         spp = args.spp
+    import wpt_dist as wdist
+    if args.scaling == "strong":
+        # one frame of `spp` samples split over the ranks; spp below is this rank's share
+        spp_total = spp
+        spp_begin, spp = wdist.spp_range_strong(rank, world, spp_total)
+        if spp == 0:
+            raise SystemExit("bench.py: --scaling strong needs at least one sample per rank")
+    else:
+        spp_total = spp * world
+        spp_begin, _ = wdist.spp_range_weak(rank, world, spp)   # disjoint, decorrelated (RNG keyed on global index)
     sd = gen()
     N = W * H
     t0 = time.perf_counter()
@@ -213,14 +223,12 @@ def run_ours(args):
     # two lanes (profiles/r1_microbench.md): every trace launch at the kernel's own occupancy (8 CTAs/SM, 64 registers)
     r.set_tuning(args.variant, args.ctas_per_sm, args.overlap)
     film = torch.zeros(3, N, device="cuda")
-    import wpt_dist as wdist
-    spp_begin, _ = wdist.spp_range_weak(rank, world, spp)   # disjoint, decorrelated (RNG keyed on global index)
 
     def step():
         film.zero_()
         r.render(cam, film, spp_begin, spp, depth, seed=SEED)
         wdist.reduce_film(film, dst=0)                          # one NCCL reduce of the partial films
-        wpt.film_scale(film, 1.0 / (spp * world))
+        wpt.film_scale(film, 1.0 / spp_total)
         return r.finish()
 
     for _ in range(args.warmup):
@@ -325,9 +333,9 @@ def run_ours(args):
     if rank == 0:
         line = {"metric": "Mrays/s (all bounces, device-timed)", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
-                           "spp": spp, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
+                           "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
@@ -353,6 +361,8 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--overlap", type=int, default=1, help="1 = two lanes on two streams (shade of one overlaps trace of the other)")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
+                    help="weak: every rank renders --spp samples; strong: --spp samples split over the ranks")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()
