@@ -5,8 +5,9 @@
 //   shade_kernel      fused miss-accumulate / attribute interpolation / frame / Lambert sample /
 //                     next-ray write with block-aggregated warp-ballot compaction
 //                     (src/main.cpp:407-424, src/accel/optix_backend.h:463-486)
-// Nothing here is a dense contraction: no tensor cores.  The traversal is an L2-latency / issue
-// bound pointer chase; the stream kernels are HBM bound.
+// Nothing here is a dense contraction: no tensor cores.  The traversal is bound by the L1 data stage
+// (one wavefront per lane of every divergent 256-bit load) together with instruction issue
+// (profiles/r1_trace_wq_ncu_64spp.txt); the stream kernels are HBM bound.
 #include "kernels.cuh"
 #include "shade_core.h"
 #include "trace_core.h"
