@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -307,7 +308,13 @@ extern "C" const char *wpt_obj_material_name(const wpt_obj *o, uint32_t i)
 extern "C" void wpt_obj_free(wpt_obj *o) { delete o; }
 
 // ------------------------------------------------------------------------------------------------
-static TraceTuning g_default_tune = {0, 0};
+// WPT_INTERSECT_CTAS (experiments only): CTAs per SM of the persistent trace kernel behind wpt_intersect
+static TraceTuning default_tune_init()
+{
+    const char *e = std::getenv("WPT_INTERSECT_CTAS");
+    return TraceTuning{0, e ? std::atoi(e) : 0};
+}
+static TraceTuning g_default_tune = default_tune_init();
 
 extern "C" int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask,
                              uint32_t mask_size, uint32_t n, const wpt_hit_streams *hits, void *stream)
