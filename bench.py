@@ -231,6 +231,25 @@ def run_ours(args):
         wpt.film_scale(film, 1.0 / spp_total)
         return r.finish()
 
+    if args.graph:
+        # launch-bound small frames: the whole frame recorded once into a CUDA graph, replayed per step
+        if world > 1:
+            raise SystemExit("bench.py: --graph is a single-GPU option")
+        step()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(graph, stream=side):
+                film.zero_()
+                r.render(cam, film, spp_begin, spp, depth, seed=SEED, stream=side)
+                wpt.film_scale(film, 1.0 / spp_total, stream=side)
+        torch.cuda.current_stream().wait_stream(side)
+
+        def step():
+            graph.replay()
+            return r.finish()
+
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -363,6 +382,7 @@ def main():
     ap.add_argument("--overlap", type=int, default=1, help="1 = two lanes on two streams (shade of one overlaps trace of the other)")
     ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
                     help="weak: every rank renders --spp samples; strong: --spp samples split over the ranks")
+    ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()

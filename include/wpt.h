@@ -173,6 +173,9 @@ int  wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm
  * host) is filled by wpt_render_finish, which synchronises. */
 int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
                float *film_r, float *film_g, float *film_b, void *stream);
+/* wpt_render may be recorded into a CUDA graph (call it between cudaStreamBeginCapture and cudaStreamEndCapture on
+ * `stream`): it only enqueues kernels, memsets and event fork/joins.  After a replay, wpt_render_finish(stream of the
+ * replay) returns the counters of that replay (ms_total = 0); it may be called after every replay. */
 int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream);
 /* film *= 1/spp (src/main.cpp:429), device, async */
 int wpt_film_scale(float *film_r, float *film_g, float *film_b, uint32_t n, float scale, void *stream);

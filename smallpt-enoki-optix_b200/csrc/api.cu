@@ -450,6 +450,7 @@ struct wpt_renderer {
     uint32_t passes = 0, launches = 0;
     int depth_in_flight = 0;
     bool in_flight = false, two_lanes_in_flight = false;
+    bool captured = false;   // the last wpt_render was recorded into a CUDA graph (stream capture)
 };
 
 extern "C" void wpt_renderer_destroy(wpt_renderer *r)
@@ -555,10 +556,17 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
 {
     if (!r || !cam || !cfg || !film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_render: null argument");
     if (int rc = check_cfg(r, cfg)) return rc;
-    if (r->in_flight) return fail(WPT_E_STATE, "wpt_render: previous render not finished (call wpt_render_finish)");
+    if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_render: previous render not finished (call wpt_render_finish)");
     const wpt_scene *s = r->scene;
     cudaStream_t st = (cudaStream_t)stream;
     WPT_CUDA(cudaSetDevice(s->device));
+    // CUDA-graph capture (cudaStreamBeginCapture / torch.cuda.graph around this call): everything below is
+    // capturable — kernel launches, memsets, and the fork/join of the two lane streams through events; only the
+    // timing events are left out (ms_total is 0 for a captured render)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    WPT_CUDA(cudaStreamIsCapturing(st, &cap));
+    const bool capturing = cap == cudaStreamCaptureStatusActive;
+    if (capturing && r->profile) return fail(WPT_E_STATE, "wpt_render: per-kernel profiling cannot be captured into a graph");
     WPT_CUDA(cudaMemsetAsync(r->live_acc, 0, sizeof(unsigned long long) * WPT_MAX_DEPTH, st));
     r->passes = 0; r->launches = 0; r->depth_in_flight = cfg->depth;
     size_t pe = 0;
@@ -582,7 +590,7 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
         pe += 2;
         return ce;
     };
-    WPT_CUDA(cudaEventRecord(r->ev_begin, st));
+    if (!capturing) WPT_CUDA(cudaEventRecord(r->ev_begin, st));
     const uint32_t N = (uint32_t)r->W * r->H;
     // overlap mode: two lanes on their own streams, forked from and joined back into `st`; each lane takes
     // every other pass of half the samples.  Per-kernel profiling
@@ -633,7 +641,8 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
         }
     }
     r->two_lanes_in_flight = two;
-    WPT_CUDA(cudaEventRecord(r->ev_end, st));
+    if (!capturing) WPT_CUDA(cudaEventRecord(r->ev_end, st));
+    r->captured = capturing;
     WPT_CUDA(cudaGetLastError());
     r->in_flight = true;
     return WPT_OK;
@@ -646,7 +655,7 @@ extern "C" int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream
     cudaStream_t st = (cudaStream_t)stream;
     WPT_CUDA(cudaSetDevice(r->scene->device));
     WPT_CUDA(cudaStreamSynchronize(st));
-    r->in_flight = false;
+    if (!r->captured) r->in_flight = false;   // a captured render may be replayed and finished any number of times
     if (!stats) return WPT_OK;
     std::memset(stats, 0, sizeof *stats);
     unsigned long long live[WPT_MAX_DEPTH];
@@ -658,7 +667,7 @@ extern "C" int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream
     }
     stats->passes = r->passes;
     stats->kernel_launches = r->launches;
-    WPT_CUDA(cudaEventElapsedTime(&stats->ms_total, r->ev_begin, r->ev_end));
+    if (!r->captured) WPT_CUDA(cudaEventElapsedTime(&stats->ms_total, r->ev_begin, r->ev_end));
     if (r->profile) {
         for (size_t k = 0; k < r->prof_kind.size(); k++) {
             float ms = 0;

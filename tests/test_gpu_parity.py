@@ -476,3 +476,41 @@ def test_deep_trees_all_stack_variants(torch_cuda):
         ref = om.intersect("bvh", o, d)
         assert (ref[0] >= 0).mean() > 0.2
         assert util.compare_hits(ref, got, f"spiral {n}") >= 0.9999
+
+
+def test_render_is_cuda_graph_capturable(torch_cuda):
+    """wpt_render only enqueues kernels, memsets and event fork/joins, so a whole frame (film zero -> render -> 1/spp)
+    can be recorded into a CUDA graph and replayed: same film, same counters, in both the serial and the two-lane mode"""
+    import torch
+    import wpt
+    sd = scenes.cornell(16, colored=True)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    W = H = 96
+    for overlap in (0, 1):
+        r = wpt.Renderer(scene, W, H, 4)
+        r.set_tuning(0, 0, overlap)
+        ref = torch.zeros(3, W * H, device="cuda")
+        r.render(cam, ref, 0, 8, 5, seed=5)
+        st_ref = r.finish()
+        wpt.film_scale(ref, 1.0 / 8)
+        film = torch.zeros(3, W * H, device="cuda")
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                film.zero_()
+                r.render(cam, film, 0, 8, 5, seed=5, stream=side)
+                wpt.film_scale(film, 1.0 / 8, stream=side)
+        torch.cuda.current_stream().wait_stream(side)
+        for _ in range(3):
+            film.fill_(7.0)
+            g.replay()
+            st = r.finish()
+            assert st["segments"] == st_ref["segments"] and st["live"] == st_ref["live"]
+            assert torch.allclose(film, ref, rtol=0, atol=1e-5)
+        # a plain render afterwards works again and is timed
+        r.render(cam, film, 0, 8, 5, seed=5)
+        assert r.finish()["ms_total"] > 0
+        r.close()
