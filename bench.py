@@ -355,6 +355,7 @@ def run_ours(args):
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
                            "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
+                           "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph),
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
