@@ -222,6 +222,7 @@ def run_ours(args):
     r = wpt.Renderer(scene, W, H, args.spp_per_pass)
     # two lanes (profiles/r1_microbench.md): every trace launch at the kernel's own occupancy (8 CTAs/SM, 64 registers)
     r.set_tuning(args.variant, args.ctas_per_sm, args.overlap)
+    r.set_depth_seeding(args.seeding)
     film = torch.zeros(3, N, device="cuda")
 
     def step():
@@ -355,7 +356,7 @@ def run_ours(args):
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
                            "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
-                           "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph),
+                           "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph), "depth_seeding": int(args.seeding),
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
@@ -384,6 +385,7 @@ def main():
     ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
                     help="weak: every rank renders --spp samples; strong: --spp samples split over the ranks")
     ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
+    ap.add_argument("--seeding", type=int, default=1, help="1 = depth seeding of the camera rays (default), 0 = off")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()

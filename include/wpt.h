@@ -153,6 +153,7 @@ typedef struct {
     uint64_t live[WPT_MAX_DEPTH];         /* rays entering bounce j, summed over passes */
     uint32_t passes, kernel_launches;
     float    ms_total, ms_raygen, ms_trace, ms_shade; /* CUDA-event times; per-kernel only if profile=1 */
+    uint64_t retraced;                    /* depth-seeded camera rays that had to be traced a second time (not in segments) */
 } wpt_stats;
 
 typedef struct wpt_renderer wpt_renderer;
@@ -162,6 +163,12 @@ int  wpt_renderer_create(const wpt_scene *s, int32_t width, int32_t height, int3
                          wpt_renderer **out);
 void wpt_renderer_destroy(wpt_renderer *r);
 int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
+/* Depth seeding of the camera rays (default on): for pinhole cameras and spp_count >= 8, wpt_render first traces one
+ * pixel-centre ray per pixel and starts the samples' camera rays with tmax = 1.02 x the 3x3-neighbourhood maximum of
+ * those hit distances; rays that find nothing inside their seed are traced again with the full interval, so hits,
+ * counters and film are those of the unseeded render.  on = 0 switches it off; on > 1 sets the margin to on/1000
+ * (a margin below 1 makes most seeds too short: only useful to exercise the second trace). */
+int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
 /* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders
  * alternate passes on two internal streams (each lane holds half of spp_per_pass in its own queues) so that
  * the HBM-bound raygen/shade kernels of one lane overlap the issue-bound trace kernel of the other.  Same

@@ -17,23 +17,33 @@ namespace wpt {
 // ------------------------------------------------------------------------------------------------
 // ray sources / hit sinks
 // ------------------------------------------------------------------------------------------------
-struct QueueIO {
+// MODE 0: plain queue records, scalar tmax.  MODE 1 (depth-seeded camera rays, api.cu wpt_render): the ray's own tmax
+// travels in b.w (bounce 0: the throughput there is 1 by construction); a ray that finds nothing inside its seed is
+// appended to retry_list.  MODE 2: the second trace of those rays — indirect = that list, full tmax.
+template <int MODE>
+struct QueueIOT {
     RayQueue q;
     int4 *hits;
     float tmin, tmax;
+    uint32_t *retry_list, *retry_count;   // MODE 1
+    const uint32_t *indirect;             // MODE 2
     __device__ __forceinline__ bool load(uint32_t i, float &ox, float &oy, float &oz, float &dx, float &dy,
                                          float &dz, float &t0, float &t1) const
     {
-        const float4 a = __ldcs(q.a + i);   // streaming: do not displace the BVH in L2
-        const float4 b = __ldcs(q.b + i);
-        ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z; t0 = tmin; t1 = tmax;
+        const uint32_t j = MODE == 2 ? indirect[i] : i;
+        const float4 a = __ldcs(q.a + j);   // streaming: do not displace the BVH in L2
+        const float4 b = __ldcs(q.b + j);
+        ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z; t0 = tmin; t1 = MODE == 1 ? b.w : tmax;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, int32_t prim, float t, float u, float v) const
     {
-        __stcs(hits + i, make_int4(prim, __float_as_int(t), __float_as_int(u), __float_as_int(v)));
+        const uint32_t j = MODE == 2 ? indirect[i] : i;
+        __stcs(hits + j, make_int4(prim, __float_as_int(t), __float_as_int(u), __float_as_int(v)));
+        if (MODE == 1 && prim < 0 && t < 1e19f) retry_list[atomicAdd(retry_count, 1u)] = j;
     }
 };
+using QueueIO = QueueIOT<0>;
 
 struct StreamIODev {
     StreamIO s;
@@ -401,6 +411,26 @@ trace_simple(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr,
     }
 }
 
+// the default kernel: 64 registers, 8 CTAs (32 warps) per SM; the stack lives in shared memory whenever the tree
+// allows (a traversal needs at most max_depth - 1 entries: C1/C2 8 levels, C3 11, C4 13)
+template <class IO>
+static void launch_trace_default(const BvhView &bvh, const IO &io, const uint32_t *n_ptr, uint32_t n_static,
+                                 uint32_t *cursor, unsigned long long *live_acc, int num_sms,
+                                 const TraceTuning &tune, cudaStream_t st)
+{
+    auto launch = [&](auto kern) {
+        int occ = tune.ctas_per_sm;
+        if (occ <= 0) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kTraceBlock, 0);
+            if (occ <= 0) occ = 4;
+        }
+        kern<<<(uint32_t)(num_sms * occ), kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+    };
+    if (bvh.max_depth <= 11u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 10>);
+    else if (bvh.max_depth <= 15u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 14>);
+    else launch(trace_wq<IO, 20, 8>);
+}
+
 template <class IO>
 static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n_ptr, uint32_t n_static,
                              uint32_t *cursor, unsigned long long *live_acc, int num_sms,
@@ -445,22 +475,29 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 11: launch(trace_wq<IO, 20, 7, false, 0, 0>); break;   // triangle loads allocate in L1 (the old default)
     case 12: launch(trace_wq<IO, 20, 8, false, 0, 2, true, 2>); break;   // test variant: two shared-memory stack rows, the rest overflows to local memory
 
-    default:   // 64 registers, 8 CTAs (32 warps) per SM; the stack lives in shared memory whenever the tree allows
-        // (a traversal needs at most max_depth - 1 entries: C1/C2 8 levels, C3 11, C4 13)
-        if (bvh.max_depth <= 11u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 10>);
-        else if (bvh.max_depth <= 15u) launch(trace_wq<IO, 20, 8, false, 0, 2, false, 14>);
-        else launch(trace_wq<IO, 20, 8>);
-        break;
+    default: launch_trace_default(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
     }
 }
 
 void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,
                         uint32_t *cursor, unsigned long long *live_acc, float tmin, float tmax,
-                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st)
+                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st,
+                        int seeded, uint32_t *retry_list, uint32_t *retry_count, const uint32_t *indirect)
 {
-    QueueIO io;
-    io.q = q; io.hits = hits; io.tmin = tmin; io.tmax = tmax;
-    launch_trace_any(bvh, io, n_ptr, n_max, cursor, live_acc, num_sms, tune, st);
+    // the seeded first trace and its second trace always run the default kernel (tune.variant applies to plain launches)
+    if (indirect) {
+        QueueIOT<2> io;
+        io.q = q; io.hits = hits; io.tmin = tmin; io.tmax = tmax; io.retry_list = nullptr; io.retry_count = nullptr; io.indirect = indirect;
+        launch_trace_default(bvh, io, n_ptr, n_max, cursor, live_acc, num_sms, tune, st);
+    } else if (seeded) {
+        QueueIOT<1> io;
+        io.q = q; io.hits = hits; io.tmin = tmin; io.tmax = tmax; io.retry_list = retry_list; io.retry_count = retry_count; io.indirect = nullptr;
+        launch_trace_default(bvh, io, n_ptr, n_max, cursor, live_acc, num_sms, tune, st);
+    } else {
+        QueueIO io;
+        io.q = q; io.hits = hits; io.tmin = tmin; io.tmax = tmax; io.retry_list = nullptr; io.retry_count = nullptr; io.indirect = nullptr;
+        launch_trace_any(bvh, io, n_ptr, n_max, cursor, live_acc, num_sms, tune, st);
+    }
 }
 
 void launch_trace_streams(const BvhView &bvh, const StreamIO &s, uint32_t n, uint32_t *cursor, int num_sms,
@@ -488,9 +525,12 @@ __device__ __forceinline__ void lane_to_pixel(uint32_t p, int W, int H, int &x, 
     }
 }
 
+// seed != nullptr: b.w carries the ray's tmax seed (seed[pixel]) instead of the constant throughput 1 — the trace and
+// shade kernels of bounce 0 are told (QueueIO::seeded, shade_kernel's seeded0).  centre != 0: one ray per pixel
+// through the pixel centre and the lens centre (the depth pre-pass; not a sample of the estimator).
 __global__ void __launch_bounds__(256)
 raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass, uint32_t k0, uint32_t k1,
-              RayQueue q, uint32_t *__restrict__ qcount0)
+              RayQueue q, uint32_t *__restrict__ qcount0, const float *__restrict__ seed, int centre)
 {
     const uint32_t N = (uint32_t)W * (uint32_t)H;
     const uint32_t total = N * (uint32_t)spp_in_pass;
@@ -502,22 +542,61 @@ raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass
         const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;   // src/main.cpp:379-381
         uint32_t rnd[4];
         philox4x32_10(pixel, (uint32_t)spp_first + s_local, 0u, 0u, k0, k1, rnd);
-        const float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
+        float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
+        if (centre) xi[0] = xi[1] = xi[2] = xi[3] = 0.5f;
         V3 o, d;
         camera_ray(cam, x, y, W, H, xi, o, d);
         __stcs(q.a + i, make_float4(o.x, o.y, o.z, __uint_as_float(pixel | (s_local << 24))));
-        __stcs(q.b + i, make_float4(d.x, d.y, d.z, 1.0f));        // contrib = 1 (src/main.cpp:391)
+        __stcs(q.b + i, make_float4(d.x, d.y, d.z, seed ? __ldg(seed + pixel) : 1.0f));   // contrib = 1 (src/main.cpp:391)
         __stcs(q.c + i, make_float2(1.0f, 1.0f));
     }
 }
 
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
-                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st)
+                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed, int centre)
 {
     const uint64_t total = (uint64_t)W * H * spp_in_pass;
     const uint32_t blocks = (uint32_t)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
     raygen_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_first, spp_in_pass, (uint32_t)seed,
-                                                       (uint32_t)(seed >> 32), q, qcount0);
+                                                       (uint32_t)(seed >> 32), q, qcount0, tmax_seed, centre);
+}
+
+// ------------------------------------------------------------------------------------------------
+// depth pre-pass -> per-pixel tmax seeds for the camera rays of a frame
+// ------------------------------------------------------------------------------------------------
+// depth[pixel] = hit distance of the pixel-centre ray (inf on a miss); the queue is in 8x4-tile order, the pixel
+// travels in a.w
+__global__ void __launch_bounds__(256)
+depth_scatter_kernel(const float4 *__restrict__ qa, const int4 *__restrict__ hits, uint32_t n, float *__restrict__ depth)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int4 h = hits[i];
+        depth[__float_as_uint(qa[i].w) & 0x00ffffffu] = h.x >= 0 ? __int_as_float(h.y) : __int_as_float(0x7f800000);
+    }
+}
+// seed[pixel] = margin * max of the 3x3 neighbourhood of depth (the jittered rays of a pixel lie inside the hull
+// of those nine centres); no seed (1e20) where any of them missed.  A wrong seed costs a second trace, never a result.
+__global__ void __launch_bounds__(256)
+depth_seed_kernel(const float *__restrict__ depth, int W, int H, float margin, float *__restrict__ seed)
+{
+    const uint32_t N = (uint32_t)W * (uint32_t)H;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < N; p += gridDim.x * blockDim.x) {
+        const int y = (int)(p / (uint32_t)W), x = (int)(p % (uint32_t)W);
+        float m = 0.0f;
+        for (int dy = -1; dy <= 1; dy++)
+            for (int dx = -1; dx <= 1; dx++) {
+                const int xx = min(max(x + dx, 0), W - 1), yy = min(max(y + dy, 0), H - 1);
+                m = fmaxf(m, depth[(uint32_t)yy * (uint32_t)W + (uint32_t)xx]);
+            }
+        seed[p] = m < 1e19f ? m * margin : 1e20f;
+    }
+}
+void launch_depth_seeds(const float4 *qa, const int4 *hits, int W, int H, float margin, float *depth, float *seed,
+                        cudaStream_t st)
+{
+    const uint32_t n = (uint32_t)W * (uint32_t)H, blocks = (n + 255) / 256 < 148u * 16u ? (n + 255) / 256 : 148u * 16u;
+    depth_scatter_kernel<<<blocks, 256, 0, st>>>(qa, hits, n, depth);
+    depth_seed_kernel<<<blocks, 256, 0, st>>>(depth, W, H, margin, seed);
 }
 
 __global__ void __launch_bounds__(256)
@@ -555,7 +634,7 @@ __global__ void __launch_bounds__(kShadeBlock)
 shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *__restrict__ n_ptr,
              const RayQueue out, uint32_t *__restrict__ n_out, const float4 *__restrict__ tri_attr,
              const float *__restrict__ albedo, int bounce, int depth, int spp_first, uint32_t k0, uint32_t k1,
-             float *__restrict__ film_r, float *__restrict__ film_g, float *__restrict__ film_b)
+             float *__restrict__ film_r, float *__restrict__ film_g, float *__restrict__ film_b, int seeded0)
 {
     __shared__ uint32_t warp_cnt[kShadeBlock / 32];
     __shared__ uint32_t block_base;
@@ -572,7 +651,8 @@ shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *_
         if (i < n) {
             const int4 h = __ldcs(hits + i);
             const float4 a = __ldcs(in.a + i);
-            const float4 b = __ldcs(in.b + i);
+            float4 b = __ldcs(in.b + i);
+            if (seeded0) b.w = 1.0f;   // bounce 0 of a seeded pass: b.w held the ray's tmax seed, the throughput is 1
             const float2 c = __ldcs(in.c + i);
             const uint32_t pid = __float_as_uint(a.w);
             const uint32_t pixel = pid & 0x00ffffffu;
@@ -624,7 +704,7 @@ shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *_
 void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
                   uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
                   int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
-                  int num_sms, cudaStream_t st)
+                  int num_sms, cudaStream_t st, int seeded0)
 {
     uint32_t blocks = (n_max + kShadeBlock - 1) / kShadeBlock;
     const uint32_t cap = (uint32_t)num_sms * 8u;
@@ -632,7 +712,7 @@ void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, c
     if (blocks == 0) blocks = 1;
     shade_kernel<<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
                                                  spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
-                                                 film_g, film_b);
+                                                 film_g, film_b, seeded0);
 }
 
 // per-function entry point: one shading step on SoA streams (parity tests)

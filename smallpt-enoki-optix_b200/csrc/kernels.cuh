@@ -22,6 +22,7 @@ struct RayQueue {
 struct PassCounters {
     uint32_t qcount[WPT_MAX_DEPTH + 1];
     uint32_t cursor[WPT_MAX_DEPTH + 1];
+    uint32_t retry_count, retry_cursor;   // seeded camera rays that found nothing inside their interval
 };
 
 struct TraceTuning {
@@ -41,17 +42,22 @@ struct StreamIO {
 
 void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const uint32_t *n_ptr,
                         uint32_t *cursor, unsigned long long *live_acc, float tmin, float tmax,
-                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st);
+                        uint32_t n_max, int num_sms, const TraceTuning &tune, cudaStream_t st,
+                        int seeded = 0, uint32_t *retry_list = nullptr, uint32_t *retry_count = nullptr,
+                        const uint32_t *indirect = nullptr);
 void launch_trace_streams(const BvhView &bvh, const StreamIO &io, uint32_t n, uint32_t *cursor, int num_sms,
                           const TraceTuning &tune, cudaStream_t st);
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
-                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st);
+                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed = nullptr,
+                   int centre = 0);
+void launch_depth_seeds(const float4 *qa, const int4 *hits, int W, int H, float margin, float *depth, float *seed,
+                        cudaStream_t st);
 void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, uint64_t seed, float *ox,
                            float *oy, float *oz, float *dx, float *dy, float *dz, cudaStream_t st);
 void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
                   uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
                   int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
-                  int num_sms, cudaStream_t st);
+                  int num_sms, cudaStream_t st, int seeded0 = 0);
 void launch_shade_streams(uint32_t n, const float *const o[3], const float *const d[3], const int32_t *tri_id,
                           const float *t, const float *u, const float *v, const float *s0, const float *s1,
                           const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],

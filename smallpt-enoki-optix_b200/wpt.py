@@ -63,7 +63,7 @@ class RenderConfig(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("segments", C.c_uint64), ("live", C.c_uint64 * WPT_MAX_DEPTH), ("passes", C.c_uint32),
                 ("kernel_launches", C.c_uint32), ("ms_total", C.c_float), ("ms_raygen", C.c_float),
-                ("ms_trace", C.c_float), ("ms_shade", C.c_float)]
+                ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("retraced", C.c_uint64)]
 
 
 _lib = None
@@ -325,6 +325,10 @@ class Renderer:
 
     def set_profile(self, on):
         _check(lib().wpt_renderer_set_profile(self._h, C.c_int(1 if on else 0)))
+
+    def set_depth_seeding(self, on=True):
+        """True / False, or an int > 1 = seed margin in thousandths (tests)"""
+        _check(lib().wpt_renderer_set_depth_seeding(self._h, C.c_int(int(on))))
 
     def set_tuning(self, trace_variant=0, ctas_per_sm=0, overlap_lanes=0):
         _check(lib().wpt_renderer_set_tuning(self._h, C.c_int(trace_variant), C.c_int(ctas_per_sm), C.c_int(overlap_lanes)))

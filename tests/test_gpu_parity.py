@@ -514,3 +514,39 @@ def test_render_is_cuda_graph_capturable(torch_cuda):
         r.render(cam, film, 0, 8, 5, seed=5)
         assert r.finish()["ms_total"] > 0
         r.close()
+
+
+def test_depth_seeding_is_exact(torch_cuda):
+    """wpt_renderer_set_depth_seeding: camera rays start with a per-pixel tmax seed from a one-ray-per-pixel
+    pre-pass; rays that find nothing inside it are traced again.  Same paths as the unseeded render: equal counters,
+    equal film up to fp32 atomic order — on a scene full of silhouettes (retries happen) and in both lane modes;
+    thin-lens cameras and short renders are not seeded at all."""
+    import torch
+    import wpt
+    for sd, W, H in ((scenes.cornell(16, colored=True), 128, 96), (scenes.knob(120, 50), 160, 128)):
+        scene = wpt.scene_from(sd)
+        cam = wpt.camera_from(sd)
+        out = {}
+        for seeding in (0, 1, 950):   # 950: seeds 5 % too short, most camera rays take the second trace
+            for overlap in (0, 1):
+                r = wpt.Renderer(scene, W, H, 8)
+                r.set_tuning(0, 0, overlap)
+                r.set_depth_seeding(seeding)
+                f = torch.zeros(3, W * H, device="cuda")
+                r.render(cam, f, 3, 16, 5, seed=21)
+                out[(seeding, overlap)] = (f, r.finish())
+                r.close()
+        f0, st0 = out[(0, 0)]
+        assert st0["retraced"] == 0
+        for key, (f, st) in out.items():
+            assert st["segments"] == st0["segments"] and st["live"] == st0["live"], key
+            assert torch.allclose(f, f0, rtol=0, atol=2e-5), key
+            if key[0] == 1:
+                assert st["retraced"] < 0.05 * st["live"][0], (key, st["retraced"])   # a few silhouette rays at most
+            if key[0] == 950:
+                assert st["retraced"] > 0.3 * st["live"][0], (key, st["retraced"])
+        # not seeded: fewer than 8 samples, or a thin lens
+        r = wpt.Renderer(scene, W, H, 4)
+        r.render(cam, torch.zeros(3, W * H, device="cuda"), 0, 4, 3, seed=1)
+        assert r.finish()["kernel_launches"] == 1 + 2 * 3
+        r.close()
