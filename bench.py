@@ -327,6 +327,8 @@ def run_ours(args):
         ab = alg_bytes(sd.n_tris)
         peak, which = measured_peak_gbs()
         n_trace = pst["passes"] * depth
+        if args.seeding and spp >= 8 and cam.c.lens_radius == 0.0:
+            n_trace += 1 + pst["passes"]      # depth pre-pass + one second-trace launch per pass (wpt_render)
         trace_s = pst["ms_trace"] * 1e-3
         achieved = pst["segments"] * ab["trace"] / trace_s / 1e9
         roof = {"bound": "hbm", "kernel": "trace_wq", "achieved": achieved, "peak": peak, "unit": "GB/s",

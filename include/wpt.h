@@ -164,9 +164,9 @@ int  wpt_renderer_create(const wpt_scene *s, int32_t width, int32_t height, int3
 void wpt_renderer_destroy(wpt_renderer *r);
 int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
 /* Depth seeding of the camera rays (default on): for pinhole cameras and spp_count >= 8, wpt_render first traces one
- * pixel-centre ray per pixel and starts the samples' camera rays with tmax = 1.02 x the 3x3-neighbourhood maximum of
+ * pixel-centre ray per pixel and starts the samples' camera rays with tmax = 1.0005 x the 3x3-neighbourhood maximum of
  * those hit distances; rays that find nothing inside their seed are traced again with the full interval, so hits,
- * counters and film are those of the unseeded render.  on = 0 switches it off; on > 1 sets the margin to on/1000
+ * counters and film are those of the unseeded render.  on = 0 switches it off; on > 1 sets the margin to on/10000
  * (a margin below 1 makes most seeds too short: only useful to exercise the second trace). */
 int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
 /* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders

@@ -435,7 +435,7 @@ struct wpt_renderer {
     // seed derived from it, W*H floats each
     float *depth = nullptr, *seed = nullptr;
     int seeding = 1;
-    float seed_margin = 1.02f;
+    float seed_margin = 1.0005f;
     // overlap mode (wpt_renderer_set_tuning, third knob): a second set of queues on its own stream; passes
     // alternate between the two lanes so that the HBM-bound shade/raygen kernels of one overlap the
     // issue-bound trace kernel of the other.  Each lane then holds half of spp_per_pass.
@@ -527,7 +527,7 @@ extern "C" int wpt_renderer_set_depth_seeding(wpt_renderer *r, int on)
     if (!r) return fail(WPT_E_INVALID, "null renderer");
     if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_renderer_set_depth_seeding: render in flight");
     r->seeding = on != 0;
-    r->seed_margin = on > 1 ? (float)on * 1e-3f : 1.02f;   // on > 1: margin in thousandths (tests force retries with < 1000)
+    r->seed_margin = on > 1 ? (float)on * 1e-4f : 1.0005f;   // on > 1: margin in 1/10000 (tests force retries with < 10000)
     return WPT_OK;
 }
 
@@ -616,7 +616,7 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     const int lane_spp = two ? (r->spp_per_pass + 1) / 2 : r->spp_per_pass;
     TraceTuning tune = r->tune;
     // depth seeding of the camera rays: one pixel-centre ray per pixel first (1/spp of the bounce-0 work), its hit
-    // distance -> a tmax seed per pixel (1.02 x the 3x3 neighbourhood maximum); the samples' camera rays then start
+    // distance -> a tmax seed per pixel (1.0005 x the 3x3 neighbourhood maximum, which already brackets the pixel); the samples' camera rays then start
     // with that tmax instead of cfg->tmax, which spares them the node visits behind the surface (simulated on C3:
     // -17..-37 %).  Exact: the closest hit inside the seed is the closest hit; the few rays that find nothing inside
     // it (silhouettes) are traced a second time with the full interval.  Pinhole cameras only (every ray of a pixel

@@ -327,7 +327,7 @@ class Renderer:
         _check(lib().wpt_renderer_set_profile(self._h, C.c_int(1 if on else 0)))
 
     def set_depth_seeding(self, on=True):
-        """True / False, or an int > 1 = seed margin in thousandths (tests)"""
+        """True / False, or an int > 1 = seed margin in 1/10000 (tests)"""
         _check(lib().wpt_renderer_set_depth_seeding(self._h, C.c_int(int(on))))
 
     def set_tuning(self, trace_variant=0, ctas_per_sm=0, overlap_lanes=0):
