@@ -616,12 +616,13 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     const int lane_spp = two ? (r->spp_per_pass + 1) / 2 : r->spp_per_pass;
     TraceTuning tune = r->tune;
     // depth seeding of the camera rays: one pixel-centre ray per pixel first (1/spp of the bounce-0 work), its hit
-    // distance -> a tmax seed per pixel (1.0005 x the 3x3 neighbourhood maximum, which already brackets the pixel); the samples' camera rays then start
-    // with that tmax instead of cfg->tmax, which spares them the node visits behind the surface (simulated on C3:
-    // -17..-37 %).  Exact: the closest hit inside the seed is the closest hit; the few rays that find nothing inside
-    // it (silhouettes) are traced a second time with the full interval.  Pinhole cameras only (every ray of a pixel
-    // then leaves the same point), and only where the pre-pass is a small fraction of the frame.
-    const bool seeded = r->seeding && cam->lens_radius == 0.0f && cfg->spp_count >= 8 && cfg->tmax >= 1e19f;
+    // distance -> a tmax seed per pixel (margin x the 3x3 neighbourhood maximum, which already brackets the pixel);
+    // the samples' camera rays then start with that tmax instead of cfg->tmax, which spares them the node visits
+    // behind the surface (simulated on C3: -22..-41 %).  Exact: the closest hit inside the seed is the closest hit;
+    // the few rays that find nothing inside it are traced a second time with the full interval.  Pinhole cameras only
+    // (every ray of a pixel leaves the same point), the reference's unbounded tmax (src/ray.h:16) only, and only
+    // where the pre-pass is a small fraction of the frame.
+    const bool seeded = r->seeding && cam->lens_radius == 0.0f && cfg->spp_count >= 8 && cfg->tmax >= 1e20f;
     if (seeded) {
         WPT_CUDA(cudaMemsetAsync(r->counters, 0, sizeof(PassCounters), st));
         WPT_CUDA(mark(0));
