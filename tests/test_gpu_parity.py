@@ -549,4 +549,9 @@ def test_depth_seeding_is_exact(torch_cuda):
         r = wpt.Renderer(scene, W, H, 4)
         r.render(cam, torch.zeros(3, W * H, device="cuda"), 0, 4, 3, seed=1)
         assert r.finish()["kernel_launches"] == 1 + 2 * 3
+        c = sd.camera
+        lens = wpt.ThinlensCamera(c["look_from"], c["look_at"], c["up"], 0.05, 3.0, c["fov_y"])
+        r.render(lens, torch.zeros(3, W * H, device="cuda"), 0, 8, 2, seed=1)
+        st = r.finish()
+        assert st["kernel_launches"] == 2 * (1 + 2 * 2) and st["retraced"] == 0
         r.close()
