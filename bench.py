@@ -5,9 +5,10 @@ terrain+spheres scene, 1920x1080, 64 spp, depth 8 — the configuration north_st
 quoted on; it fits one GPU).
 
 One step = one whole 64-spp frame through the hot path (raygen -> depth x (trace, shade)), film
-resident in HBM.  N>1 (torchrun, one rank per GPU): weak scaling — every rank renders its own
-disjoint 64-spp range [64*rank, 64*rank+64) of the same estimator and the partial films are summed
-onto rank 0 with one NCCL reduce per step, inside the timed region.
+resident in HBM.  N>1 (torchrun, one rank per GPU): configs[2] literally — the SAME 64-spp frame split
+over the ranks (strong scaling: rank g renders the global sample indices [g*64/N, (g+1)*64/N) of all
+pixels) and the partial films summed onto rank 0 with one NCCL reduce per step (wpt_film_reduce of the C
+ABI), inside the timed region.  --scaling weak gives every rank its own 64 samples instead.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1..C5]
 
@@ -33,6 +34,8 @@ for p in (PKG, os.path.join(ROOT, "oracle")):
         sys.path.insert(0, p)
 
 SEED = 0x5EED
+# one string for both arms: the driver divides the two lines only if metric, unit and direction agree
+METRIC = "Mrays/s (all bounces, device-timed)"
 
 
 def measured_peak_gbs():
@@ -64,13 +67,17 @@ def alg_bytes(n_tris):
 
 
 def traffic_per_launch(rays_per_launch):
-    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture
-    (profiles/r1_trace_traffic.json: measured bytes per ray x the rays one launch processes)"""
-    try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r1_trace_traffic.json")))
-        return float(t["dram_bytes_per_ray_weighted"]) * rays_per_launch
-    except Exception:
-        return None
+    """dram bytes per launch of the dominant kernel, DERIVED from the newest committed ncu --set full capture
+    (profiles/r*_trace_traffic.json: measured dram__bytes per ray x the rays one launch processes here).
+    Returns (bytes, source file) — the line says where the number comes from."""
+    import glob
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_trace_traffic.json")), reverse=True):
+        try:
+            t = json.load(open(f))
+            return float(t["dram_bytes_per_ray_weighted"]) * rays_per_launch, os.path.relpath(f, ROOT)
+        except Exception:
+            continue
+    return None, None
 
 
 class ClockSampler:
@@ -165,11 +172,12 @@ def run_reference(args):
     tot = sum(times)
     val = segs / tot / 1e6
     sample = f"{args.workload} scene ({sd.n_tris} tris) {W}x{H}, depth {depth}, {sample_spp} spp per step (of {spp})"
-    line = {"impl": "reference", "metric": "Mrays/s (all bounces)", "value": val, "unit": "Mrays/s",
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
-                       "spp": spp, "depth": depth, "sample": sample},
+                       "spp": spp, "depth": depth, "spp_per_step": sample_spp, "sample": sample,
+                       "timing": "host steady clock around the render (a CPU arm has no device clock); BVH build outside"},
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -190,14 +198,18 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — libwpt has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
+    import wpt_dist as wdist
+    reducer = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # the data plane's own communicator inside libwpt.so; torch.distributed ships its 128-byte id and
+        # does the barrier / max-over-ranks bookkeeping only
+        reducer = wdist.FilmReducer(local)
 
     gen, W, H, spp, depth = workload(args.workload)
     if args.spp:
         spp = args.spp
-    import wpt_dist as wdist
     if args.scaling == "strong":
         # one frame of `spp` samples split over the ranks; spp below is this rank's share
         spp_total = spp
@@ -223,19 +235,19 @@ def run_ours(args):
     # two lanes (profiles/r1_microbench.md): every trace launch at the kernel's own occupancy (8 CTAs/SM, 64 registers)
     r.set_tuning(args.variant, args.ctas_per_sm, args.overlap)
     r.set_depth_seeding(args.seeding)
+    r.set_tail(args.tail)
     film = torch.zeros(3, N, device="cuda")
 
     def step():
         film.zero_()
         r.render(cam, film, spp_begin, spp, depth, seed=SEED)
-        wdist.reduce_film(film, dst=0)                          # one NCCL reduce of the partial films
+        if reducer is not None:
+            reducer.reduce(film, 0)                             # ONE ncclReduce of the partial films (wpt_film_reduce)
         wpt.film_scale(film, 1.0 / spp_total)
         return r.finish()
 
     if args.graph:
-        # launch-bound small frames: the whole frame recorded once into a CUDA graph, replayed per step
-        if world > 1:
-            raise SystemExit("bench.py: --graph is a single-GPU option")
+        # launch-bound small frames: the whole frame (and the reduce) recorded once into a CUDA graph, replayed per step
         step()
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
@@ -244,6 +256,8 @@ def run_ours(args):
             with torch.cuda.graph(graph, stream=side):
                 film.zero_()
                 r.render(cam, film, spp_begin, spp, depth, seed=SEED, stream=side)
+                if reducer is not None:
+                    reducer.reduce(film, 0, stream=side)
                 wpt.film_scale(film, 1.0 / spp_total, stream=side)
         torch.cuda.current_stream().wait_stream(side)
 
@@ -284,23 +298,40 @@ def run_ours(args):
     if args.quick:
         if rank == 0:
             print(json.dumps({"quick": True, "value": value, "unit": "Mrays/s", "ms_per_step": ms / args.steps,
-                              "n_gpus": world, "gpu_launches": launches, "clocks": clocks}), flush=True)
+                              "n_gpus": world, "gpu_launches": launches, "clocks": clocks,
+                              "variant": args.variant, "tail": args.tail, "overlap": args.overlap}), flush=True)
         if world > 1:
+            reducer.close()
             dist.destroy_process_group()
         return 0
 
-    # ---- e2e: same metric through the host-buffer entry point (film zero -> render -> scale -> D2H)
-    host_film = np.empty((3, N), np.float32)
-    r.render_host(cam, spp_begin, min(spp, 4), depth, seed=SEED, out=host_film)
+    # ---- e2e: the same frame through the host-buffer entry points, host clock around everything: film zero ->
+    # render -> (N>1: reduce onto rank 0) -> 1/spp -> D2H of the planar film into PINNED host memory
+    pinned = wpt.PinnedArray((3, N))
+    host_film = pinned.array
+    e_steps = max(1, min(args.steps, 5))
+
+    def e2e_step():
+        if world == 1:
+            _, st = r.render_host(cam, spp_begin, spp, depth, seed=SEED, out=host_film)     # wpt_render_host
+            return st
+        film.zero_()
+        r.render(cam, film, spp_begin, spp, depth, seed=SEED)
+        reducer.reduce(film, 0)
+        if rank == 0:
+            wpt.film_scale(film, 1.0 / spp_total)
+            torch.from_numpy(host_film).copy_(film, non_blocking=True)      # pinned destination: plain DMA
+        return r.finish()                                                     # synchronises the stream
+
+    e2e_step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e_t0 = time.perf_counter()
     e_segs = 0
-    e_steps = max(1, min(args.steps, 3))
     for _ in range(e_steps):
-        _, st = r.render_host(cam, spp_begin, spp, depth, seed=SEED, out=host_film)
-        e_segs += st["segments"]
+        e_segs += e2e_step()["segments"]
+    torch.cuda.synchronize()
     e_dt = time.perf_counter() - e_t0
     et = torch.tensor([e_dt, float(e_segs)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -311,8 +342,11 @@ def run_ours(args):
         e_segs_all = float(e_segs)
     e2e = {"value": e_segs_all / e_dt / 1e6, "unit": "Mrays/s",
            "h2d_bytes_per_step": C.sizeof(wpt.Camera) + C.sizeof(wpt.RenderConfig),
-           "d2h_bytes_per_step": 3 * N * 4,
-           "what": "wpt_render_host: host camera/config in, film zero + full frame + 1/spp + D2H of the planar film"}
+           "d2h_bytes_per_step": 3 * N * 4, "ms_per_frame": 1e3 * e_dt / e_steps, "steps": e_steps,
+           "what": ("wpt_render_host: host camera/config in, film zero + full frame + 1/spp + D2H of the planar film "
+                    "into pinned host memory" if world == 1 else
+                    "per rank: film zero + this rank's samples; wpt_film_reduce onto rank 0; rank 0: 1/spp + D2H of the "
+                    "reduced film into pinned host memory; host clock, max over ranks")}
 
     # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
     roof = None
@@ -326,18 +360,32 @@ def run_ours(args):
         r.set_profile(False)
         ab = alg_bytes(sd.n_tris)
         peak, which = measured_peak_gbs()
-        n_trace = pst["passes"] * depth
+        tail = args.tail if args.tail != 0 else 2
+        wave = tail if 1 <= tail < depth else depth
+        n_trace = pst["passes"] * (wave + (1 if wave < depth else 0))
         if args.seeding and spp >= 8 and cam.c.lens_radius == 0.0:
             n_trace += 1 + pst["passes"]      # depth pre-pass + one second-trace launch per pass (wpt_render)
         trace_s = pst["ms_trace"] * 1e-3
         achieved = pst["segments"] * ab["trace"] / trace_s / 1e9
+        traffic, traffic_src = traffic_per_launch(pst["segments"] / n_trace)
+        shade_s = pst["ms_shade"] * 1e-3
+        shaded = sum(pst["live"][:wave])           # segments that went through shade_kernel (the fused tail shades its own)
         roof = {"bound": "hbm", "kernel": "trace_wq", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "peak_source": which, "traffic": traffic_per_launch(pst["segments"] / n_trace),
+                "frac": achieved / peak, "peak_source": which, "traffic": traffic, "traffic_source": traffic_src,
+                "traffic_note": "derived: dram__bytes per ray of the committed ncu --set full capture x this run's rays per launch",
+                "algorithmic_yardstick": True,
+                "binding_limit": "instruction issue + L1 data-stage wavefronts (ncu, profiles/); the BVH is L2 resident, so "
+                                 "`achieved` counts ALGORITHMIC bytes (SURVEY §8d), not DRAM traffic",
                 "alg_bytes_per_ray": ab["trace"], "rays_per_launch": pst["segments"] / n_trace,
                 "avg_launch_ms": pst["ms_trace"] / n_trace, "launches": n_trace,
                 "trace_mrays_s": pst["segments"] / trace_s / 1e6,
+                "trace_time_includes": "depth pre-pass, second traces and (fused tail) the in-kernel shading of bounces >= %d" % wave,
                 "share_of_step": {"raygen": pst["ms_raygen"] / pst["ms_total"], "trace": pst["ms_trace"] / pst["ms_total"],
                                   "shade": pst["ms_shade"] / pst["ms_total"]},
+                "shade": {"kernel": "shade_kernel", "bound": "hbm", "alg_bytes_per_ray": ab["shade"],
+                          "achieved": shaded * ab["shade"] / max(shade_s, 1e-9) / 1e9,
+                          "frac": shaded * ab["shade"] / max(shade_s, 1e-9) / 1e9 / peak, "segments": shaded,
+                          "ms": pst["ms_shade"]},
                 "pipeline": {"alg_bytes_per_ray": ab["pipeline"],
                              "achieved": value / world * 1e6 * ab["pipeline"] / 1e9,
                              "frac": value / world * 1e6 * ab["pipeline"] / 1e9 / peak},
@@ -353,12 +401,14 @@ def run_ours(args):
                "sample": f"same scene/camera, {W}x{H}, depth {depth}, {k} spp of {spp} ({seg} segments, {dt:.1f} s)"}
 
     if rank == 0:
-        line = {"metric": "Mrays/s (all bounces, device-timed)", "value": value, "unit": "Mrays/s", "n_gpus": world,
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
-                           "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass, "parallelism": f"spp-shard x{world}",
+                           "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass,
+                           "parallelism": f"spp-shard x{world}", "reduce": "wpt_film_reduce (ncclReduce, own communicator)" if world > 1 else None,
                            "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph), "depth_seeding": int(args.seeding),
+                           "fused_tail_from": args.tail if args.tail != 0 else 2, "trace_variant": args.variant,
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
@@ -368,6 +418,7 @@ def run_ours(args):
                 "commit_s": commit_s}
         print(json.dumps(line), flush=True)
     if world > 1:
+        reducer.close()
         dist.destroy_process_group()
     return 0
 
@@ -384,8 +435,9 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--overlap", type=int, default=1, help="1 = two lanes on two streams (shade of one overlaps trace of the other)")
-    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
-                    help="weak: every rank renders --spp samples; strong: --spp samples split over the ranks")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="strong",
+                    help="strong (default): the frame's --spp samples split over the ranks; weak: every rank renders --spp samples")
+    ap.add_argument("--tail", type=int, default=0, help="fused tail from this bounce on (0 = default, -1 = off)")
     ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
     ap.add_argument("--seeding", type=int, default=1, help="1 = depth seeding of the camera rays (default), 0 = off")
     ap.add_argument("--no-cpu", action="store_true")

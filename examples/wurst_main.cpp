@@ -3,7 +3,8 @@
 // normalise, write wurst.pfm.  Same statement order; the per-sample / per-bounce loop body
 // (main.cpp:385-426) is the one call PathLoop::render.
 //
-//   wurst [scene.obj] [out.pfm] [width height num_samples num_bounces] [--kd]
+//   wurst [scene.obj] [out.pfm] [width height num_samples num_bounces] [--kd] [--gpus N]
+// --gpus N shards the samples over N GPUs of the box (ShardedPathLoop: one wpt_film_reduce per frame), no Python.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -24,7 +25,38 @@ int main(int argc, char **argv)
     const int num_samples = argc > 5 ? std::atoi(argv[5]) : 100;
     const int num_bounces = argc > 6 ? std::atoi(argv[6]) : 2;
     bool use_kd = false;
-    for (int i = 1; i < argc; i++) use_kd = use_kd || std::strcmp(argv[i], "--kd") == 0;
+    int n_gpus = 1;
+    for (int i = 1; i < argc; i++) {
+        use_kd = use_kd || std::strcmp(argv[i], "--kd") == 0;
+        if (std::strcmp(argv[i], "--gpus") == 0 && i + 1 < argc) n_gpus = std::atoi(argv[i + 1]);
+    }
+    if (n_gpus > 1) {
+        try {
+            // the same main(), samples sharded over n_gpus GPUs: every GPU commits its own copy of the scene
+            wpt_obj *o = nullptr;
+            check(wpt_obj_load(obj, use_kd ? 1 : 0, &o));
+            wpt_mesh_desc d;
+            check(wpt_obj_mesh(o, &d));
+            ShardedPathLoop loop(d, n_gpus, width, height);
+            wpt_obj_free(o);
+            Film film(width, height);
+            StopWatch sw;
+            sw.reset();
+            const float pi = 3.14159265358979323846f;
+            const ThinlensCamera thinlens(Real3(0.0f, 3.03f, 5.0f), Real3(0.0f, 0.03f, 0.0f), Real3(0.0f, 1.0f, 0.0f), 0.00f,
+                                          1.0f, 40.0f / 180.0f * pi);
+            const uint64_t segments = loop.render(thinlens, num_samples, num_bounces, film);
+            std::cout << sw.timeMilliSec() << std::endl;
+            std::cerr << segments << " ray segments on " << n_gpus << " GPUs" << std::endl;
+            std::cout << "writing image" << std::endl;
+            Fimage::save_pfm(film.r.data(), film.g.data(), film.b.data(), width, height, out);
+            std::cout << "done" << std::endl;
+        } catch (const std::exception &e) {
+            std::cerr << e.what() << std::endl;
+            return 1;
+        }
+        return 0;
+    }
     try {
         // load meshes and materials (src/main.cpp:364-366)
         Scene scene;

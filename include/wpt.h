@@ -13,12 +13,13 @@
  */
 #ifndef WPT_H
 #define WPT_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define WPT_VERSION 100
+#define WPT_VERSION 200
 
 enum {
     WPT_OK = 0,
@@ -64,8 +65,13 @@ typedef struct {
 } wpt_bvh_stats;
 
 int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
+/* Optional texture coordinates (src/main.cpp:215-223: texcoords f32[2*n_uvs], texcoord_triplets i32[3*n_triangles],
+ * -1 = none): only wpt_hit_attributes reads them.  Call before wpt_scene_commit. */
+int  wpt_scene_set_texcoords(wpt_scene *s, const float *uvs, const int32_t *uv_triplets, uint32_t n_uvs);
 /* SAH BVH build on the host, flatten to 64-byte 7-wide quantised nodes + 64-byte triangle blocks (one buffer),
- * one upload to `device`. */
+ * one upload to `device`.  WPT_E_LIMIT if the tree is deeper than 32 levels or holds more than 2^27 blocks
+ * (nodes + triangles; about 115 M triangles).  If the vertices were last moved by wpt_scene_refit_device, a
+ * re-commit rebuilds from those device-side positions (read back first). */
 int  wpt_scene_commit(wpt_scene *s, int device);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
 /* Moved vertices, same topology: bottom-up refit of the node boxes and rewrite of the triangle blocks ON THE
@@ -74,7 +80,9 @@ int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
  * quality decays with the deformation; commit again to rebuild.  Vertex normals are kept; faces that shade
  * with the geometric normal get the new one.  wpt_scene_refit takes HOST positions f32[3*n_positions]
  * (count must match; synchronous); wpt_scene_refit_device takes a DEVICE array and is asynchronous on
- * `stream` (the host copy used by a later wpt_scene_commit is then NOT updated). */
+ * `stream`; the caller orders it against renders in flight on other streams (the refit rewrites the blocks the
+ * traversal reads).  Device-side positions are not validated: a NaN/Inf vertex yields an undefined tree until the
+ * next wpt_scene_commit, which reads the positions back and rejects non-finite ones. */
 int  wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions);
 int  wpt_scene_refit_device(wpt_scene *s, const float *d_positions, void *stream);
 void wpt_scene_destroy(wpt_scene *s);
@@ -118,11 +126,32 @@ typedef struct {
     float   *t, *u, *v;
 } wpt_hit_streams;
 
+/* Per-ray tmin below 0 is clamped to 0 (the closest hit is folded with an integer min on the float bits of t).
+ * At most 4096 wpt_intersect calls of one scene may be in flight at the same time (ring of fetch cursors).
+ * Equal-t hits (shared edges) resolve to the LOWEST primitive index, whatever the order of the tests. */
 int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
                   uint32_t n, const wpt_hit_streams *hits, void *stream);
 /* Same, HOST buffers in and out (copies inside; synchronous). */
 int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
                        uint32_t n, const wpt_hit_streams *hits);
+
+/* ------------------------------------------------------------------ derived hit attributes
+ * What OptixBackend::intersect returns WITH the hit (src/accel/optix_backend.h:463-486, TriangleHitInfo :99-134) and
+ * Scene::intersect turns into an Interaction (src/main.cpp:320-340): position o + t d, geometry normal
+ * normalize(cross(p1-p0, p2-p0)) (src/add_math.h:9-16), barycentric-interpolated UN-normalised shading normal and
+ * texcoord (src/add_math.h:3-7), and the material index (src/main.cpp:325).  DEVICE streams; an output group
+ * (p*, gn*, sn*, t*) is either given completely or left NULL; lanes with tri_id < 0 are left untouched.
+ * Faces without normals get the geometric normal as shading normal (the deviation stated above); scenes without
+ * texcoords yield (0, 0). */
+typedef struct {
+    float *px, *py, *pz;
+    float *gnx, *gny, *gnz;
+    float *snx, *sny, *snz;
+    float *tu, *tv;
+    int32_t *material_id;
+} wpt_hit_attr_streams;
+int wpt_hit_attributes(const wpt_scene *s, const wpt_ray_streams *rays, const wpt_hit_streams *hits, uint32_t n,
+                       const wpt_hit_attr_streams *out, void *stream);
 
 /* ------------------------------------------------------------------ camera (src/pinhole.h:7-72) */
 typedef struct {
@@ -169,6 +198,12 @@ int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
  * counters and film are those of the unseeded render.  on = 0 switches it off; on > 1 sets the margin to on/10000
  * (a margin below 1 makes most seeds too short: only useful to exercise the second trace). */
 int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
+/* Fused tail: bounces >= first_bounce of every pass run in ONE launch of the traversal kernel with the shading step
+ * fused in (a path whose segment ends is shaded by its own lane and continues in place) instead of one trace + one
+ * shade launch per bounce — late bounces hold few paths and a persistent launch has a fixed ramp-up/drain cost.
+ * Same Philox counters, same paths, same film up to fp32 atomic order.  first_bounce >= 1; 0 = default (2);
+ * negative = off (a wavefront launch pair for every bounce). */
+int  wpt_renderer_set_tail(wpt_renderer *r, int first_bounce);
 /* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders
  * alternate passes on two internal streams (each lane holds half of spp_per_pass in its own queues) so that
  * the HBM-bound raygen/shade kernels of one lane overlap the issue-bound trace kernel of the other.  Same
@@ -186,9 +221,46 @@ int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *
 int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream);
 /* film *= 1/spp (src/main.cpp:429), device, async */
 int wpt_film_scale(float *film_r, float *film_g, float *film_b, uint32_t n, float scale, void *stream);
-/* Whole frame, HOST film out (zero -> render -> scale 1/spp_count -> D2H), src/main.cpp:369-439. */
+/* Whole frame, HOST film out (zero -> render -> scale 1/spp_count -> D2H), src/main.cpp:369-439.  The three
+ * channel copies are queued asynchronously behind the frame and waited for once; give it a film from wpt_host_alloc
+ * (pinned) and they are plain DMA transfers. */
 int wpt_render_host(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
                     float *film_r, float *film_g, float *film_b, wpt_stats *stats);
+
+/* pinned host memory (cudaMallocHost) for films and ray buffers that cross the boundary every frame */
+int  wpt_host_alloc(size_t bytes, void **out);
+void wpt_host_free(void *p);
+
+/* device buffers for hosts without CUDA headers of their own (include/wpt_shim.hpp); the reference's Enoki arrays
+ * do this for it (enoki/cuda.h:210-220).  upload is asynchronous on `stream`, download synchronises it. */
+int  wpt_device_count(void);
+int  wpt_device_alloc(int device, size_t bytes, void **out);
+void wpt_device_free(void *p);
+int  wpt_device_upload(void *dst_device, const void *src_host, size_t bytes, void *stream);
+int  wpt_device_download(void *dst_host, const void *src_device, size_t bytes, void *stream);
+int  wpt_device_sync(int device);            /* makes `device` current and waits for all its work */
+int  wpt_device_set(int device);             /* makes `device` current (the stream-level calls act on the current device) */
+int  wpt_device_zero(void *dst_device, size_t bytes, void *stream);
+
+/* ------------------------------------------------------------------ multi-GPU: one reduce of the partial films
+ * GPU g renders the global sample indices [g*spp/G, (g+1)*spp/G) of ALL pixels (spp_begin/spp_count of
+ * wpt_render_config; the RNG is keyed on the global index), the scene is replicated, and the only exchange is ONE
+ * sum of the partial films onto `root` — ncclReduce(sum, f32) over NVLink — followed by wpt_film_scale(1/spp) there.
+ * The reference is single-GPU (src/main.cpp:354-446); this is what its main() calls once per frame when sharded
+ * (examples/wurst_main.cpp --gpus N).  NCCL is bound at run time (dlopen libnccl.so.2); WPT_E_STATE if absent.
+ *   one process per GPU:  rank 0: wpt_nccl_unique_id(id) -> ship the 128 bytes to the other ranks by any means
+ *                         every rank: wpt_nccl_comm_create(id, n_ranks, rank, device, &comm)
+ *   one process, N GPUs:  wpt_nccl_comm_create_all(N, devices, comms); the N wpt_film_reduce calls of a frame go
+ *                         between wpt_nccl_group_start() and wpt_nccl_group_end()
+ * wpt_film_reduce is asynchronous on `stream` and in place: afterwards the root's film holds the sum (one collective
+ * of 3n floats when the three planes are contiguous, a group of three otherwise). */
+int  wpt_nccl_unique_id(void *id128);
+int  wpt_nccl_comm_create(const void *id128, int n_ranks, int rank, int device, void **comm);
+int  wpt_nccl_comm_create_all(int n_devices, const int *devices, void **comms);
+void wpt_nccl_comm_destroy(void *comm);
+int  wpt_nccl_group_start(void);
+int  wpt_nccl_group_end(void);
+int  wpt_film_reduce(void *nccl_comm, float *film_r, float *film_g, float *film_b, uint32_t n, int root, void *stream);
 
 /* ------------------------------------------------------------------ per-function device entry points
  * (parity tests of the fused kernels' pieces against the oracle; all DEVICE buffers) */

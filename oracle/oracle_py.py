@@ -163,6 +163,17 @@ class Mesh:
         u = np.full(n, np.nan, np.float32)
         v = np.full(n, np.nan, np.float32)
         fn, ctx = self.backend(kind)
+        if isinstance(tmin, np.ndarray) or isinstance(tmax, np.ndarray):
+            # per-ray windows (src/ray.h:20-26): both as float32 arrays of n
+            assert mask is None
+            tmin = np.ascontiguousarray(np.broadcast_to(np.asarray(tmin, np.float32), (n,)))
+            tmax = np.ascontiguousarray(np.broadcast_to(np.asarray(tmax, np.float32), (n,)))
+            lib().orc_intersect_streams_win(C.c_void_p(fn), C.c_void_p(ctx),
+                                            *[c.ctypes.data_as(C.c_void_p) for c in cols],
+                                            tmin.ctypes.data_as(C.c_void_p), tmax.ctypes.data_as(C.c_void_p), C.c_uint32(n),
+                                            hid.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p),
+                                            u.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p), C.c_int(threads))
+            return hid, t, u, v
         if mask is None:
             mptr, msz = None, 0
         else:

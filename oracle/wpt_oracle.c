@@ -435,6 +435,25 @@ void orc_intersect_streams(orc_intersect1_fn fn, void *ctx,
     }
 }
 
+/* the same with per-ray windows: struct Params carries tmin / tmax as ARRAYS (src/optixdata.h:20-21, filled from
+ * Ray3C::m_tmin / m_tmax, src/ray.h:20-26; read per lane at wavefront_isect.cu:98-99) */
+void orc_intersect_streams_win(orc_intersect1_fn fn, void *ctx,
+                               const float *ox, const float *oy, const float *oz,
+                               const float *dx, const float *dy, const float *dz,
+                               const float *tmin, const float *tmax, uint32_t n,
+                               int32_t *id, float *t, float *u, float *v, int threads)
+{
+    if (threads <= 0) threads = orc_num_threads();
+#pragma omp parallel for schedule(dynamic, 1024) num_threads(threads)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        const float o[3] = { ox[i], oy[i], oz[i] }, d[3] = { dx[i], dy[i], dz[i] };
+        int32_t hid = -1; float ht = 0, hu = 0, hv = 0;
+        fn(ctx, o, d, tmin[i], tmax[i], &hid, &ht, &hu, &hv);
+        id[i] = hid;
+        if (hid >= 0) { t[i] = ht; u[i] = hu; v[i] = hv; }
+    }
+}
+
 /* ------------------------------------------------------------------ shading step
  * optix_backend.h:469 (p = o + t d), :483-484 (interpolated, un-normalised shading normal),
  * main.cpp:325-326 (material), :414-424 (frame, Lambert sample, next ray). */
@@ -466,6 +485,36 @@ void orc_shade_step(const orc_mesh *m, const float o[3], const float d[3], int32
     orc_frame_to_world(fr, local, next_d);
     const int32_t mat = m->mat_id ? m->mat_id[tri] : 0;
     for (int k = 0; k < 3; k++) weight[k] = m->albedo ? m->albedo[3 * mat + k] : 1.0f;
+}
+
+/* optix_backend.h:463-486 + main.cpp:325; faces without normals: the documented deviation of orc_shade_step */
+void orc_hit_attributes(const orc_mesh *m, const float *uvs, const int32_t *uv_idx, const float o[3], const float d[3],
+                        int32_t tri, float t, float u, float v, float p[3], float gn[3], float sn[3], float uv[2],
+                        int32_t *mat)
+{
+    for (int k = 0; k < 3; k++) p[k] = o[k] + t * d[k];                                     /* :469 */
+    const float *p0 = m->pos + 3 * (size_t)m->pos_idx[3 * tri], *p1 = m->pos + 3 * (size_t)m->pos_idx[3 * tri + 1],
+                *p2 = m->pos + 3 * (size_t)m->pos_idx[3 * tri + 2];
+    orc_geometry_normal(p0, p1, p2, gn);                                                    /* :472-476 */
+    if (m->nrm && m->nrm_idx && m->nrm_idx[3 * tri] >= 0 && m->nrm_idx[3 * tri + 1] >= 0 && m->nrm_idx[3 * tri + 2] >= 0) {
+        orc_barycentric3(m->nrm + 3 * (size_t)m->nrm_idx[3 * tri], m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 1],
+                         m->nrm + 3 * (size_t)m->nrm_idx[3 * tri + 2], u, v, sn);           /* :483-484 */
+    } else {
+        const float e1[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] };
+        const float e2[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
+        float g[3] = { e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0] };
+        const float l = sqrtf(g[0] * g[0] + g[1] * g[1] + g[2] * g[2]);
+        if (l > 0) { g[0] /= l; g[1] /= l; g[2] /= l; } else { g[0] = 0; g[1] = 1; g[2] = 0; }
+        orc_barycentric3(g, g, g, u, v, sn);
+    }
+    uv[0] = uv[1] = 0.0f;
+    if (uvs && uv_idx && uv_idx[3 * tri] >= 0 && uv_idx[3 * tri + 1] >= 0 && uv_idx[3 * tri + 2] >= 0) {    /* :479-480 */
+        const float w = 1.0f - u - v;
+        for (int k = 0; k < 2; k++)
+            uv[k] = w * uvs[2 * (size_t)uv_idx[3 * tri] + k] + u * uvs[2 * (size_t)uv_idx[3 * tri + 1] + k] +
+                    v * uvs[2 * (size_t)uv_idx[3 * tri + 2] + k];
+    }
+    *mat = m->mat_id ? m->mat_id[tri] : 0;                                                  /* main.cpp:325 */
 }
 
 /* ------------------------------------------------------------------ the loop (main.cpp:376-429)

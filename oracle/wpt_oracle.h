@@ -102,6 +102,13 @@ void orc_intersect_streams(orc_intersect1_fn fn, void *ctx,
                            float tmin, float tmax, const uint8_t *mask, uint32_t mask_size, uint32_t n,
                            int32_t *id, float *t, float *u, float *v, int threads);
 
+/* per-ray windows (src/optixdata.h:20-21, src/ray.h:20-26) */
+void orc_intersect_streams_win(orc_intersect1_fn fn, void *ctx,
+                               const float *ox, const float *oy, const float *oz,
+                               const float *dx, const float *dy, const float *dz,
+                               const float *tmin, const float *tmax, uint32_t n,
+                               int32_t *id, float *t, float *u, float *v, int threads);
+
 /* ---------------- the loop ---------------- */
 enum { ORC_RNG_PCG32 = 0, ORC_RNG_PHILOX = 1 };
 typedef struct {
@@ -121,6 +128,14 @@ uint64_t orc_render(const orc_mesh *m, orc_intersect1_fn fn, void *ctx, const or
  * and two uniforms, return next origin, next direction, and the bsdf weight. */
 void orc_shade_step(const orc_mesh *m, const float o[3], const float d[3], int32_t tri, float t, float u,
                     float v, const float s[2], float next_o[3], float next_d[3], float weight[3]);
+
+/* The derived hit attributes OptixBackend::intersect returns with a hit (src/accel/optix_backend.h:463-486):
+ * position o + t d (:469), geometry normal (:472-476, add_math.h:9-16), barycentric-interpolated shading normal
+ * (:483-484) and texcoord (:479-480; uvs f32[2*n], uv_idx i32[3*n_tris], either may be NULL -> (0,0)), and the
+ * material index Scene::intersect gathers (src/main.cpp:325). */
+void orc_hit_attributes(const orc_mesh *m, const float *uvs, const int32_t *uv_idx, const float o[3], const float d[3],
+                        int32_t tri, float t, float u, float v, float p[3], float gn[3], float sn[3], float uv[2],
+                        int32_t *mat);
 
 int orc_num_threads(void);
 #ifdef __cplusplus

@@ -1,5 +1,8 @@
 // api.cu — the C ABI of libwpt.so (include/wpt.h).  Host C++; owns device memory, never throws.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>   // types and prototypes only: the library is bound with dlopen (wpt_film_reduce)
+#include <nvtx3/nvToolsExt.h>
 
 #include <atomic>
 #include <chrono>
@@ -30,31 +33,39 @@ static int fail(int code, const std::string &msg)
             return fail(WPT_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
     } while (0)
 
+// NVTX ranges around the host-side phases (visible in Nsight Systems / ncu --nvtx; no-ops without a tool attached)
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
 extern "C" const char *wpt_last_error(void) { return g_err.c_str(); }
 extern "C" int wpt_version(void) { return WPT_VERSION; }
 
 // ------------------------------------------------------------------------------------------------
+constexpr uint32_t kCursorRing = 4096;
 struct wpt_scene {
     // host copies (src/main.cpp:296-309 keeps them in Enoki arrays)
-    std::vector<float> pos, nrm, albedo;
-    std::vector<int32_t> pidx, nidx, mat;
+    std::vector<float> pos, nrm, albedo, uvs;
+    std::vector<int32_t> pidx, nidx, mat, uvidx;
     uint32_t n_tris = 0;
+    bool pos_on_device_newer = false;   // wpt_scene_refit_device moved the vertices: the next commit reads them back
     // device
     int device = -1, num_sms = 0;
     bool committed = false;
     Block64 *d_blocks = nullptr;   // nodes and triangles, bvh.h
     TriAttr48 *d_attr = nullptr;
     float *d_albedo = nullptr;
-    // ray-fetch cursors of wpt_intersect: a ring of 64, one per call, so that calls on different streams
-    // (the BVH is read-only) do not share a counter
+    // ray-fetch cursors of wpt_intersect: a ring of kCursorRing, one per call, so that calls on different streams
+    // (the BVH is read-only) do not share a counter; more than kCursorRing calls in flight at once would alias
     uint32_t *d_cursor = nullptr;
     mutable std::atomic<uint32_t> cursor_rr{0};
     // refit (wpt_scene_refit): BFS levels of the node blocks, geometric-normal flags; vertex/index/box
     // buffers are allocated by the first refit
     uint32_t *d_level_nodes = nullptr;
     uint8_t *d_geo = nullptr;
-    float *d_pos = nullptr, *d_boxes = nullptr;
-    int32_t *d_pidx = nullptr;
+    float *d_pos = nullptr, *d_boxes = nullptr, *d_uvs = nullptr;
+    int32_t *d_pidx = nullptr, *d_uvidx = nullptr;
     std::vector<uint32_t> level_begin;
     BvhView view{};
     wpt_bvh_stats stats{};
@@ -97,6 +108,8 @@ static void scene_free_device(wpt_scene *s)
     cudaFree(s->d_blocks); cudaFree(s->d_attr);
     cudaFree(s->d_albedo); cudaFree(s->d_cursor);
     cudaFree(s->d_level_nodes); cudaFree(s->d_geo); cudaFree(s->d_pos); cudaFree(s->d_boxes); cudaFree(s->d_pidx);
+    cudaFree(s->d_uvs); cudaFree(s->d_uvidx);
+    s->d_uvs = nullptr; s->d_uvidx = nullptr;
     s->d_blocks = nullptr; s->d_attr = nullptr;
     s->d_albedo = nullptr; s->d_cursor = nullptr;
     s->d_level_nodes = nullptr; s->d_geo = nullptr; s->d_pos = nullptr; s->d_boxes = nullptr; s->d_pidx = nullptr;
@@ -117,12 +130,26 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail(WPT_E_CUDA, "wpt_scene_commit: no CUDA device (libwpt has no CPU fallback)");
     if (device < 0 || device >= ndev) return fail(WPT_E_INVALID, "wpt_scene_commit: bad device index");
-    if (s->committed) scene_free_device(s);
+    if (s->committed) {
+        if (s->pos_on_device_newer && s->d_pos) {
+            // the vertices were last moved by wpt_scene_refit_device: rebuild from those, not from the stale host copy
+            WPT_CUDA(cudaSetDevice(s->device));
+            WPT_CUDA(cudaMemcpy(s->pos.data(), s->d_pos, s->pos.size() * sizeof(float), cudaMemcpyDeviceToHost));
+            for (float x : s->pos)
+                if (!std::isfinite(x)) return fail(WPT_E_INVALID, "wpt_scene_commit: non-finite vertex in the device-side positions");
+        }
+        scene_free_device(s);
+    }
+    s->pos_on_device_newer = false;
+    NvtxRange nvtx_commit("wpt_scene_commit");
 
     BuiltBvh b;
     const char *err = nullptr;
     if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
         return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
+    // the warp queue of trace_wq packs (owner lane << 27 | block index) into one word
+    if (!blocks_within_limit(b.blocks.size()))
+        return fail(WPT_E_LIMIT, "wpt_scene_commit: more than 2^27 BVH blocks (about 115 M triangles)");
 
     // per-ORIGINAL-triangle shading attributes: 3 vertex normals + material, one 48 B gather per hit
     std::vector<TriAttr48> attr(s->n_tris);
@@ -163,7 +190,7 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     WPT_CUDA(cudaMalloc(&s->d_blocks, b.blocks.size() * sizeof(Block64)));
     WPT_CUDA(cudaMalloc(&s->d_attr, attr.size() * sizeof(TriAttr48)));
     WPT_CUDA(cudaMalloc(&s->d_albedo, s->albedo.size() * sizeof(float)));
-    WPT_CUDA(cudaMalloc(&s->d_cursor, 64 * sizeof(uint32_t)));
+    WPT_CUDA(cudaMalloc(&s->d_cursor, kCursorRing * sizeof(uint32_t)));
     WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -172,6 +199,17 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     WPT_CUDA(cudaMemcpy(s->d_level_nodes, b.level_nodes.data(), b.level_nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_geo, geo.data(), geo.size(), cudaMemcpyHostToDevice));
     s->level_begin = b.level_begin;
+    // vertex positions and index triplets: refit (csrc/refit.cu) and wpt_hit_attributes (geometry normal)
+    WPT_CUDA(cudaMalloc(&s->d_pos, s->pos.size() * sizeof(float)));
+    WPT_CUDA(cudaMalloc(&s->d_pidx, s->pidx.size() * sizeof(int32_t)));
+    WPT_CUDA(cudaMemcpy(s->d_pos, s->pos.data(), s->pos.size() * sizeof(float), cudaMemcpyHostToDevice));
+    WPT_CUDA(cudaMemcpy(s->d_pidx, s->pidx.data(), s->pidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    if (!s->uvs.empty()) {
+        WPT_CUDA(cudaMalloc(&s->d_uvs, s->uvs.size() * sizeof(float)));
+        WPT_CUDA(cudaMalloc(&s->d_uvidx, s->uvidx.size() * sizeof(int32_t)));
+        WPT_CUDA(cudaMemcpy(s->d_uvs, s->uvs.data(), s->uvs.size() * sizeof(float), cudaMemcpyHostToDevice));
+        WPT_CUDA(cudaMemcpy(s->d_uvidx, s->uvidx.data(), s->uvidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
     WPT_CUDA(cudaDeviceSynchronize());
     const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 
@@ -206,11 +244,7 @@ extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
 // refit for moved vertices (same topology): csrc/refit.cu
 static int refit_common(wpt_scene *s, const float *d_positions, cudaStream_t st)
 {
-    if (!s->d_boxes) {
-        WPT_CUDA(cudaMalloc(&s->d_boxes, (size_t)s->view.n_blocks * 6 * sizeof(float)));
-        WPT_CUDA(cudaMalloc(&s->d_pidx, s->pidx.size() * sizeof(int32_t)));
-        WPT_CUDA(cudaMemcpy(s->d_pidx, s->pidx.data(), s->pidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-    }
+    if (!s->d_boxes) WPT_CUDA(cudaMalloc(&s->d_boxes, (size_t)s->view.n_blocks * 6 * sizeof(float)));
     launch_refit(s->d_blocks, s->d_level_nodes, s->level_begin.data(), (uint32_t)s->level_begin.size() - 1, d_positions,
                  s->d_pidx, s->d_boxes, s->d_attr, s->d_geo, st);
     WPT_CUDA(cudaGetLastError());
@@ -222,7 +256,11 @@ extern "C" int wpt_scene_refit_device(wpt_scene *s, const float *d_positions, vo
     if (!s || !d_positions) return fail(WPT_E_INVALID, "wpt_scene_refit_device: null argument");
     if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_refit_device: scene not committed");
     WPT_CUDA(cudaSetDevice(s->device));
-    return refit_common(s, d_positions, (cudaStream_t)stream);
+    // keep the scene's own device copy current (wpt_hit_attributes reads it; the next wpt_scene_commit reads it back)
+    if (d_positions != s->d_pos)
+        WPT_CUDA(cudaMemcpyAsync(s->d_pos, d_positions, s->pos.size() * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    s->pos_on_device_newer = true;
+    return refit_common(s, s->d_pos, (cudaStream_t)stream);
 }
 
 extern "C" int wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions)
@@ -233,8 +271,8 @@ extern "C" int wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_
     for (size_t k = 0; k < s->pos.size(); k++)
         if (!std::isfinite(positions[k])) return fail(WPT_E_INVALID, "wpt_scene_refit: non-finite vertex");
     WPT_CUDA(cudaSetDevice(s->device));
-    if (!s->d_pos) WPT_CUDA(cudaMalloc(&s->d_pos, s->pos.size() * sizeof(float)));
     s->pos.assign(positions, positions + s->pos.size());
+    s->pos_on_device_newer = false;
     WPT_CUDA(cudaMemcpy(s->d_pos, positions, s->pos.size() * sizeof(float), cudaMemcpyHostToDevice));
     if (int rc = refit_common(s, s->d_pos, nullptr)) return rc;
     WPT_CUDA(cudaDeviceSynchronize());
@@ -333,7 +371,7 @@ extern "C" int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, co
     io.tmin = rays->tmin; io.tmax = rays->tmax; io.tmin_s = rays->tmin_scalar; io.tmax_s = rays->tmax_scalar;
     io.mask = mask; io.mask_size = mask_size;
     io.tri_id = hits->tri_id; io.t = hits->t; io.u = hits->u; io.v = hits->v;
-    uint32_t *cursor = s->d_cursor + (s->cursor_rr.fetch_add(1u, std::memory_order_relaxed) & 63u);
+    uint32_t *cursor = s->d_cursor + (s->cursor_rr.fetch_add(1u, std::memory_order_relaxed) & (kCursorRing - 1u));
     WPT_CUDA(cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st));
     launch_trace_streams(s->view, io, n, cursor, s->num_sms, g_default_tune, st);
     WPT_CUDA(cudaGetLastError());
@@ -422,6 +460,7 @@ extern "C" int wpt_camera_init(wpt_camera *c, const float from[3], const float a
 // ------------------------------------------------------------------------------------------------
 // renderer: the sample/bounce loop (src/main.cpp:385-426) as a wavefront pipeline
 // ------------------------------------------------------------------------------------------------
+constexpr int kDefaultTailFrom = 2;   // measured on C3 (profiles/r2_*); <= 0 = no fused tail
 struct wpt_renderer {
     const wpt_scene *scene = nullptr;
     int W = 0, H = 0, spp_per_pass = 1;
@@ -436,6 +475,8 @@ struct wpt_renderer {
     float *depth = nullptr, *seed = nullptr;
     int seeding = 1;
     float seed_margin = 1.0005f;
+    // fused tail (wpt_renderer_set_tail): bounces >= tail_from of a pass run in ONE launch of trace_wq<TailIO>
+    int tail_from = kDefaultTailFrom;
     // overlap mode (wpt_renderer_set_tuning, third knob): a second set of queues on its own stream; passes
     // alternate between the two lanes so that the HBM-bound shade/raygen kernels of one overlap the
     // issue-bound trace kernel of the other.  Each lane then holds half of spp_per_pass.
@@ -531,6 +572,14 @@ extern "C" int wpt_renderer_set_depth_seeding(wpt_renderer *r, int on)
     return WPT_OK;
 }
 
+extern "C" int wpt_renderer_set_tail(wpt_renderer *r, int first_bounce)
+{
+    if (!r) return fail(WPT_E_INVALID, "null renderer");
+    if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_renderer_set_tail: render in flight");
+    r->tail_from = first_bounce == 0 ? kDefaultTailFrom : first_bounce;
+    return WPT_OK;
+}
+
 extern "C" int wpt_renderer_set_tuning(wpt_renderer *r, int trace_variant, int ctas_per_sm, int overlap_lanes)
 {
     if (!r) return fail(WPT_E_INVALID, "null renderer");
@@ -576,6 +625,7 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_render: previous render not finished (call wpt_render_finish)");
     const wpt_scene *s = r->scene;
     cudaStream_t st = (cudaStream_t)stream;
+    NvtxRange nvtx_render("wpt_render");
     WPT_CUDA(cudaSetDevice(s->device));
     // CUDA-graph capture (cudaStreamBeginCapture / torch.cuda.graph around this call): everything below is
     // capturable — kernel launches, memsets, and the fork/join of the two lane streams through events; only the
@@ -659,7 +709,8 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
                       seeded ? r->seed : nullptr, 0);
         WPT_CUDA(done());
         r->launches++;
-        for (int j = 0; j < cfg->depth; j++) {
+        const int wave_end = (r->tail_from >= 1 && r->tail_from < cfg->depth) ? r->tail_from : cfg->depth;
+        for (int j = 0; j < wave_end; j++) {
             const RayQueue &qin = q[j & 1], &qout = q[(j + 1) & 1];
             const bool sj = seeded && j == 0;
             // the retry list of bounce 0 borrows the c stream of the queue that shade 0 fills afterwards
@@ -680,6 +731,19 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
                          cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, ls, sj);
             WPT_CUDA(done());
             r->launches += 2;
+        }
+        if (wave_end < cfg->depth) {
+            // every remaining bounce of this pass in one launch: paths are shaded and continued in place
+            TailArgs ta;
+            ta.tmin = cfg->tmin; ta.tmax = cfg->tmax;
+            ta.tri_attr = reinterpret_cast<const float4 *>(s->d_attr); ta.albedo = s->d_albedo;
+            ta.film_r = film_r; ta.film_g = film_g; ta.film_b = film_b;
+            ta.bounce0 = wave_end; ta.depth = cfg->depth; ta.spp_first = spp_first; ta.seed = cfg->seed;
+            WPT_CUDA(mark(1));
+            launch_trace_tail(s->view, q[wave_end & 1], &counters->qcount[wave_end], &counters->cursor[wave_end], live_acc,
+                              ta, n_max, s->num_sms, tune, ls);
+            WPT_CUDA(done());
+            r->launches++;
         }
         r->passes++;
     }
@@ -737,11 +801,74 @@ extern "C" int wpt_film_scale(float *film_r, float *film_g, float *film_b, uint3
     return WPT_OK;
 }
 
+// Pinned host memory through the ABI: a film allocated here makes the three copies at the end of wpt_render_host
+// asynchronous DMA transfers at PCIe/NVLink-C2C speed (a pageable destination is staged by the driver in chunks)
+extern "C" int wpt_host_alloc(size_t bytes, void **out)
+{
+    if (!out || bytes == 0) return fail(WPT_E_INVALID, "wpt_host_alloc: bad argument");
+    WPT_CUDA(cudaMallocHost(out, bytes));
+    return WPT_OK;
+}
+extern "C" void wpt_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+// device buffers through the ABI, so that a C++ host (include/wpt_shim.hpp) needs no CUDA headers of its own — the
+// reference's Enoki arrays allocate and copy for it (enoki/cuda.h:210-220)
+extern "C" int wpt_device_alloc(int device, size_t bytes, void **out)
+{
+    if (!out || bytes == 0) return fail(WPT_E_INVALID, "wpt_device_alloc: bad argument");
+    WPT_CUDA(cudaSetDevice(device));
+    WPT_CUDA(cudaMalloc(out, bytes));
+    return WPT_OK;
+}
+extern "C" void wpt_device_free(void *p)
+{
+    if (p) cudaFree(p);
+}
+extern "C" int wpt_device_upload(void *dst_device, const void *src_host, size_t bytes, void *stream)
+{
+    if (!dst_device || !src_host) return fail(WPT_E_INVALID, "wpt_device_upload: null argument");
+    WPT_CUDA(cudaMemcpyAsync(dst_device, src_host, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return WPT_OK;
+}
+extern "C" int wpt_device_download(void *dst_host, const void *src_device, size_t bytes, void *stream)
+{
+    if (!dst_host || !src_device) return fail(WPT_E_INVALID, "wpt_device_download: null argument");
+    WPT_CUDA(cudaMemcpyAsync(dst_host, src_device, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    WPT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return WPT_OK;
+}
+extern "C" int wpt_device_sync(int device)
+{
+    WPT_CUDA(cudaSetDevice(device));
+    WPT_CUDA(cudaDeviceSynchronize());
+    return WPT_OK;
+}
+extern "C" int wpt_device_set(int device)
+{
+    WPT_CUDA(cudaSetDevice(device));
+    return WPT_OK;
+}
+extern "C" int wpt_device_zero(void *dst_device, size_t bytes, void *stream)
+{
+    if (!dst_device) return fail(WPT_E_INVALID, "wpt_device_zero: null argument");
+    WPT_CUDA(cudaMemsetAsync(dst_device, 0, bytes, (cudaStream_t)stream));
+    return WPT_OK;
+}
+extern "C" int wpt_device_count(void)
+{
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+
 extern "C" int wpt_render_host(wpt_renderer *r, const wpt_camera *cam, const wpt_render_config *cfg,
                                float *film_r, float *film_g, float *film_b, wpt_stats *stats)
 {
     if (!r || !cam || !cfg || !film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_render_host: null argument");
     if (int rc = check_cfg(r, cfg)) return rc;
+    NvtxRange nvtx_host("wpt_render_host");
     const size_t N = (size_t)r->W * r->H;
     WPT_CUDA(cudaSetDevice(r->scene->device));
     float *dr = r->film, *dg = r->film + N, *db = r->film + 2 * N;
@@ -749,10 +876,11 @@ extern "C" int wpt_render_host(wpt_renderer *r, const wpt_camera *cam, const wpt
     if (int rc = wpt_render(r, cam, cfg, dr, dg, db, nullptr)) return rc;
     if (cfg->spp_count > 0)
         if (int rc = wpt_film_scale(dr, dg, db, (uint32_t)N, 1.0f / (float)cfg->spp_count, nullptr)) return rc;
+    // src/main.cpp:437-439: three planar channels to the host, queued behind the frame; ONE synchronisation
+    WPT_CUDA(cudaMemcpyAsync(film_r, dr, sizeof(float) * N, cudaMemcpyDeviceToHost, nullptr));
+    WPT_CUDA(cudaMemcpyAsync(film_g, dg, sizeof(float) * N, cudaMemcpyDeviceToHost, nullptr));
+    WPT_CUDA(cudaMemcpyAsync(film_b, db, sizeof(float) * N, cudaMemcpyDeviceToHost, nullptr));
     if (int rc = wpt_render_finish(r, stats, nullptr)) return rc;
-    WPT_CUDA(cudaMemcpy(film_r, dr, sizeof(float) * N, cudaMemcpyDeviceToHost));   // src/main.cpp:437-439
-    WPT_CUDA(cudaMemcpy(film_g, dg, sizeof(float) * N, cudaMemcpyDeviceToHost));
-    WPT_CUDA(cudaMemcpy(film_b, db, sizeof(float) * N, cudaMemcpyDeviceToHost));
     return WPT_OK;
 }
 
@@ -786,6 +914,162 @@ extern "C" int wpt_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, ui
 {
     if (!out) return fail(WPT_E_INVALID, "wpt_philox: null output");
     launch_philox(n, c1, c2, key, out, (cudaStream_t)stream);
+    WPT_CUDA(cudaGetLastError());
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-GPU: ONE reduce of the partial films.  NCCL is bound at run time (dlopen of libnccl.so.2:
+// the copy already in the process — e.g. the one PyTorch loaded — or the system one), so libwpt.so itself has no
+// link-time dependency on it and single-GPU hosts need no NCCL at all.
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommInitAll) CommInitAll = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclReduce) Reduce = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+};
+}  // namespace
+static NcclApi g_nccl;
+static int nccl_load()
+{
+    if (g_nccl.lib) return WPT_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(WPT_E_STATE, std::string("NCCL not available: ") + dlerror());
+    auto sym = [&](const char *n) { return dlsym(h, n); };
+    g_nccl.GetUniqueId = reinterpret_cast<decltype(g_nccl.GetUniqueId)>(sym("ncclGetUniqueId"));
+    g_nccl.CommInitRank = reinterpret_cast<decltype(g_nccl.CommInitRank)>(sym("ncclCommInitRank"));
+    g_nccl.CommInitAll = reinterpret_cast<decltype(g_nccl.CommInitAll)>(sym("ncclCommInitAll"));
+    g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(sym("ncclCommDestroy"));
+    g_nccl.Reduce = reinterpret_cast<decltype(g_nccl.Reduce)>(sym("ncclReduce"));
+    g_nccl.GroupStart = reinterpret_cast<decltype(g_nccl.GroupStart)>(sym("ncclGroupStart"));
+    g_nccl.GroupEnd = reinterpret_cast<decltype(g_nccl.GroupEnd)>(sym("ncclGroupEnd"));
+    g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(sym("ncclGetErrorString"));
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce ||
+        !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.GetErrorString)
+        return fail(WPT_E_STATE, "NCCL library lacks a required symbol");
+    g_nccl.lib = h;
+    return WPT_OK;
+}
+#define WPT_NCCL(call)                                                                              \
+    do {                                                                                            \
+        ncclResult_t e_ = (call);                                                                   \
+        if (e_ != ncclSuccess) return fail(WPT_E_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(e_)); \
+    } while (0)
+
+extern "C" int wpt_nccl_unique_id(void *id128)
+{
+    if (!id128) return fail(WPT_E_INVALID, "wpt_nccl_unique_id: null argument");
+    if (int rc = nccl_load()) return rc;
+    static_assert(sizeof(ncclUniqueId) == 128, "wpt_nccl_unique_id hands out 128 bytes");
+    WPT_NCCL(g_nccl.GetUniqueId(reinterpret_cast<ncclUniqueId *>(id128)));
+    return WPT_OK;
+}
+
+extern "C" int wpt_nccl_comm_create(const void *id128, int n_ranks, int rank, int device, void **comm)
+{
+    if (!id128 || !comm || n_ranks <= 0 || rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_nccl_comm_create: bad argument");
+    if (int rc = nccl_load()) return rc;
+    WPT_CUDA(cudaSetDevice(device));
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof id);
+    WPT_NCCL(g_nccl.CommInitRank(reinterpret_cast<ncclComm_t *>(comm), n_ranks, id, rank));
+    return WPT_OK;
+}
+
+extern "C" int wpt_nccl_comm_create_all(int n_devices, const int *devices, void **comms)
+{
+    if (n_devices <= 0 || !comms) return fail(WPT_E_INVALID, "wpt_nccl_comm_create_all: bad argument");
+    if (int rc = nccl_load()) return rc;
+    WPT_NCCL(g_nccl.CommInitAll(reinterpret_cast<ncclComm_t *>(comms), n_devices, devices));
+    return WPT_OK;
+}
+
+extern "C" void wpt_nccl_comm_destroy(void *comm)
+{
+    if (comm && g_nccl.lib) g_nccl.CommDestroy(reinterpret_cast<ncclComm_t>(comm));
+}
+
+extern "C" int wpt_nccl_group_start(void)
+{
+    if (int rc = nccl_load()) return rc;
+    WPT_NCCL(g_nccl.GroupStart());
+    return WPT_OK;
+}
+extern "C" int wpt_nccl_group_end(void)
+{
+    if (int rc = nccl_load()) return rc;
+    WPT_NCCL(g_nccl.GroupEnd());
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_reduce(void *nccl_comm, float *film_r, float *film_g, float *film_b, uint32_t n, int root,
+                               void *stream)
+{
+    if (!nccl_comm || !film_r || !film_g || !film_b) return fail(WPT_E_INVALID, "wpt_film_reduce: null argument");
+    if (int rc = nccl_load()) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    ncclComm_t comm = reinterpret_cast<ncclComm_t>(nccl_comm);
+    if (film_g == film_r + n && film_b == film_g + n) {
+        // the usual planar film [3][W*H]: one collective of 3n floats, in place
+        WPT_NCCL(g_nccl.Reduce(film_r, film_r, (size_t)3 * n, ncclFloat32, ncclSum, root, comm, st));
+    } else {
+        WPT_NCCL(g_nccl.GroupStart());
+        WPT_NCCL(g_nccl.Reduce(film_r, film_r, n, ncclFloat32, ncclSum, root, comm, st));
+        WPT_NCCL(g_nccl.Reduce(film_g, film_g, n, ncclFloat32, ncclSum, root, comm, st));
+        WPT_NCCL(g_nccl.Reduce(film_b, film_b, n, ncclFloat32, ncclSum, root, comm, st));
+        WPT_NCCL(g_nccl.GroupEnd());
+    }
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// derived hit attributes (src/accel/optix_backend.h:463-486, src/main.cpp:325)
+extern "C" int wpt_scene_set_texcoords(wpt_scene *s, const float *uvs, const int32_t *uv_triplets, uint32_t n_uvs)
+{
+    if (!s) return fail(WPT_E_INVALID, "wpt_scene_set_texcoords: null scene");
+    if (s->committed) return fail(WPT_E_STATE, "wpt_scene_set_texcoords: call before wpt_scene_commit");
+    if (!uvs || !uv_triplets || n_uvs == 0) { s->uvs.clear(); s->uvidx.clear(); return WPT_OK; }
+    for (size_t k = 0; k < 3 * (size_t)s->n_tris; k++)
+        if (uv_triplets[k] >= (int32_t)n_uvs) return fail(WPT_E_INVALID, "texcoord index out of range");
+    s->uvs.assign(uvs, uvs + 2 * (size_t)n_uvs);
+    s->uvidx.assign(uv_triplets, uv_triplets + 3 * (size_t)s->n_tris);
+    return WPT_OK;
+}
+
+extern "C" int wpt_hit_attributes(const wpt_scene *s, const wpt_ray_streams *rays, const wpt_hit_streams *hits,
+                                  uint32_t n, const wpt_hit_attr_streams *out, void *stream)
+{
+    if (!s || !rays || !hits || !out) return fail(WPT_E_INVALID, "wpt_hit_attributes: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_hit_attributes: scene not committed");
+    if (n == 0) return WPT_OK;
+    if (!hits->tri_id || !hits->u || !hits->v) return fail(WPT_E_INVALID, "wpt_hit_attributes: tri_id, u, v required");
+    const bool want_p = out->px || out->py || out->pz, want_g = out->gnx || out->gny || out->gnz,
+               want_s = out->snx || out->sny || out->snz, want_t = out->tu || out->tv;
+    if ((want_p && !(out->px && out->py && out->pz)) || (want_g && !(out->gnx && out->gny && out->gnz)) ||
+        (want_s && !(out->snx && out->sny && out->snz)) || (want_t && !(out->tu && out->tv)))
+        return fail(WPT_E_INVALID, "wpt_hit_attributes: an output group must be given completely or not at all");
+    if (want_p && !(rays->ox && rays->oy && rays->oz && rays->dx && rays->dy && rays->dz && hits->t))
+        return fail(WPT_E_INVALID, "wpt_hit_attributes: position needs the ray streams and t");
+    WPT_CUDA(cudaSetDevice(s->device));
+    HitAttrArgs a;
+    a.ox = rays->ox; a.oy = rays->oy; a.oz = rays->oz; a.dx = rays->dx; a.dy = rays->dy; a.dz = rays->dz;
+    a.tri_id = hits->tri_id; a.t = hits->t; a.u = hits->u; a.v = hits->v;
+    a.pos = s->d_pos; a.pidx = s->d_pidx; a.tri_attr = reinterpret_cast<const float4 *>(s->d_attr);
+    a.uvs = s->d_uvs; a.uvidx = s->d_uvidx;
+    a.p[0] = out->px; a.p[1] = out->py; a.p[2] = out->pz;
+    a.ng[0] = out->gnx; a.ng[1] = out->gny; a.ng[2] = out->gnz;
+    a.ns[0] = out->snx; a.ns[1] = out->sny; a.ns[2] = out->snz;
+    a.uv[0] = out->tu; a.uv[1] = out->tv;
+    a.mat = out->material_id;
+    launch_hit_attributes(n, a, (cudaStream_t)stream);
     WPT_CUDA(cudaGetLastError());
     return WPT_OK;
 }

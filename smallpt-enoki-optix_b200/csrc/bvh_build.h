@@ -23,6 +23,11 @@ struct BuiltBvh {
 bool build_bvh7(const float *positions, uint32_t n_pos, const int32_t *triplets, uint32_t n_tris,
                 BuiltBvh &out, const char **err, int threads = 0);
 
+// The warp queue of the default trace kernel packs (owner lane << 27 | block index) into one 32-bit word
+// (csrc/trace_kernels.cu), so a flattened tree may hold at most 2^27 blocks (8.6 GB; about 115 M triangles).
+constexpr uint64_t kMaxBlocks = 1ull << 27;
+inline bool blocks_within_limit(uint64_t n_blocks) { return n_blocks <= kMaxBlocks; }
+
 // Decode helpers shared with the tests
 uint32_t node_imask(const Node7 &n);
 uint32_t node_tri_count(const Node7 &n, int slot);

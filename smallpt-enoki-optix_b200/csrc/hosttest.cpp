@@ -132,6 +132,9 @@ int wpt_hosttest_trace_stats(const float *pos, uint32_t n_pos, const int32_t *id
     return 0;
 }
 
+// the block-count limit wpt_scene_commit enforces (bvh_build.h)
+int wpt_hosttest_blocks_within_limit(uint64_t n_blocks) { return blocks_within_limit(n_blocks) ? 1 : 0; }
+
 int wpt_hosttest_trace(const float *pos, uint32_t n_pos, const int32_t *idx, uint32_t n_tris,
                        const float *ox, const float *oy, const float *oz, const float *dx, const float *dy,
                        const float *dz, float tmin, float tmax, uint32_t n,

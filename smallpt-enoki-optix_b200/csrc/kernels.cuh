@@ -26,8 +26,35 @@ struct PassCounters {
 };
 
 struct TraceTuning {
-    int variant;      // 0 = persistent + dynamic fetch (default), 1 = one thread per ray
-    int ctas_per_sm;  // persistent grid = num_sms * ctas_per_sm
+    int variant;      // 0 = warp-queue kernel (default); the others are comparison / experiment variants, trace_kernels.cu
+    int ctas_per_sm;  // persistent grid = num_sms * ctas_per_sm (0 = the occupancy calculator's answer)
+};
+// defaults of the warp-queue kernel (measured, profiles/r2_*): refill threshold (lanes), flush scheme (1 = balanced)
+constexpr int kDefaultThresh = 20;
+constexpr int kDefaultFlush = 1;
+
+// the fused tail (trace_wq<TailIO>): everything shade_kernel needs, for all remaining bounces of a pass
+struct TailArgs {
+    float tmin, tmax;
+    const float4 *tri_attr;
+    const float *albedo;
+    float *film_r, *film_g, *film_b;
+    int bounce0, depth, spp_first;
+    uint64_t seed;
+};
+
+// wpt_hit_attributes (src/accel/optix_backend.h:463-486): device streams; any output group may be null
+struct HitAttrArgs {
+    const float *ox, *oy, *oz, *dx, *dy, *dz;
+    const int32_t *tri_id;
+    const float *t, *u, *v;
+    const float *pos;
+    const int32_t *pidx;
+    const float4 *tri_attr;
+    const float *uvs;
+    const int32_t *uvidx;
+    float *p[3], *ng[3], *ns[3], *uv[2];
+    int32_t *mat;
 };
 
 // SoA stream front-end of wpt_intersect (mirror of struct Params, src/optixdata.h:11-29)
@@ -47,6 +74,10 @@ void launch_trace_queue(const BvhView &bvh, const RayQueue &q, int4 *hits, const
                         const uint32_t *indirect = nullptr);
 void launch_trace_streams(const BvhView &bvh, const StreamIO &io, uint32_t n, uint32_t *cursor, int num_sms,
                           const TraceTuning &tune, cudaStream_t st);
+void launch_trace_tail(const BvhView &bvh, const RayQueue &q, const uint32_t *n_ptr, uint32_t *cursor,
+                       unsigned long long *live_acc, const TailArgs &a, uint32_t n_max, int num_sms,
+                       const TraceTuning &tune, cudaStream_t st);
+void launch_hit_attributes(uint32_t n, const HitAttrArgs &a, cudaStream_t st);
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
                    const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed = nullptr,
                    int centre = 0);

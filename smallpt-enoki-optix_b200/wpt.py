@@ -49,6 +49,11 @@ class HitStreams(C.Structure):
     _fields_ = [("tri_id", C.c_void_p), ("t", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p)]
 
 
+class HitAttrStreams(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("px", "py", "pz", "gnx", "gny", "gnz", "snx", "sny", "snz", "tu", "tv",
+                                          "material_id")]
+
+
 class Camera(C.Structure):
     _fields_ = [("origin", C.c_float * 3), ("x", C.c_float * 3), ("y", C.c_float * 3), ("z", C.c_float * 3),
                 ("film_size_y", C.c_float), ("focal_dist", C.c_float), ("fov_y", C.c_float),
@@ -83,6 +88,10 @@ def lib():
         L.wpt_obj_mesh.argtypes = [C.c_void_p, C.c_void_p]
         L.wpt_obj_texcoords.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.wpt_obj_material_name.argtypes = [C.c_void_p, C.c_uint32]
+        L.wpt_host_alloc.argtypes = [C.c_size_t, C.c_void_p]
+        L.wpt_host_free.argtypes = [C.c_void_p]
+        L.wpt_nccl_comm_destroy.argtypes = [C.c_void_p]
+        L.wpt_film_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -170,13 +179,36 @@ def load_meshes(path, use_kd=False):
     return out
 
 
+class PinnedArray:
+    """float32 numpy array over pinned host memory from wpt_host_alloc (freed with the object)"""
+
+    def __init__(self, shape):
+        n = int(np.prod(shape))
+        self._p = C.c_void_p()
+        _check(lib().wpt_host_alloc(C.c_size_t(4 * n), C.byref(self._p)))
+        buf = (C.c_float * n).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=np.float32).reshape(shape)
+
+    def __del__(self):
+        try:
+            if self._p:
+                self.array = None
+                lib().wpt_host_free(self._p)
+                self._p = C.c_void_p()
+        except Exception:
+            pass
+
+
 def scene_from_obj(path, device=0, use_kd=False):
     """main()'s load_meshes -> Scene::add_triangle_mesh -> commit (src/main.cpp:362-366)"""
     m = load_meshes(path, use_kd)
     s = Scene()
     has_n = m["normals"].size > 0
+    has_t = m["texcoords"].size > 0
     s.add_triangle_mesh(m["positions"], m["position_triplets"], m["normals"] if has_n else None,
-                        m["normal_triplets"] if has_n else None, m["material_id"], m["albedo"])
+                        m["normal_triplets"] if has_n else None, m["material_id"], m["albedo"],
+                        texcoords=m["texcoords"] if has_t else None,
+                        texcoord_triplets=m["texcoord_triplets"] if has_t else None)
     s.commit(device)
     return s
 
@@ -191,7 +223,7 @@ class Scene:
         self.n_triangles = 0
 
     def add_triangle_mesh(self, positions, position_triplets, normals=None, normal_triplets=None,
-                          material_id=None, albedo=None):
+                          material_id=None, albedo=None, texcoords=None, texcoord_triplets=None):
         """Host arrays as produced by load_meshes (src/main.cpp:133-251); see also wpt_obj.load_meshes."""
         if self._h:
             raise WptError(3, "Scene already holds a mesh")
@@ -216,6 +248,12 @@ class Scene:
             keep.append(alb)
         _check(lib().wpt_scene_create(C.byref(d), C.byref(self._h)))
         self.n_triangles = d.n_triangles
+        if texcoords is not None and texcoord_triplets is not None:
+            uv = _np(texcoords, np.float32).reshape(-1)
+            uvi = _np(texcoord_triplets, np.int32).reshape(-1)
+            assert uvi.size == idx.size
+            _check(lib().wpt_scene_set_texcoords(self._h, C.c_void_p(uv.ctypes.data), C.c_void_p(uvi.ctypes.data),
+                                                 C.c_uint32(uv.size // 2)))
 
     def commit(self, device=0):
         if not self._h:
@@ -253,11 +291,7 @@ class Scene:
                    torch.full((n,), float("nan"), dtype=torch.float32, device=dev),
                    torch.full((n,), float("nan"), dtype=torch.float32, device=dev),
                    torch.full((n,), float("nan"), dtype=torch.float32, device=dev))
-        rs = RayStreams(*[t_.data_ptr() for t_ in list(origin) + list(direction)], None, None, tmin, tmax)
-        if torch.is_tensor(tmin):
-            rs.tmin = tmin.data_ptr()
-        if torch.is_tensor(tmax):
-            rs.tmax = tmax.data_ptr()
+        rs = self._ray_streams(origin, direction, tmin, tmax)
         hs = HitStreams(*[t_.data_ptr() for t_ in out])
         mptr, msz = None, 0
         if active is not None:
@@ -267,6 +301,44 @@ class Scene:
             mptr, msz = C.c_void_p(active.data_ptr()), active.numel()
         _check(lib().wpt_intersect(self._h, C.byref(rs), mptr, C.c_uint32(msz), C.c_uint32(n), C.byref(hs),
                                    _stream_handle(stream)))
+        return out
+
+    @staticmethod
+    def _ray_streams(origin, direction, tmin=1e-3, tmax=1e20):
+        """struct Params' eight ray streams (src/optixdata.h:11-29): tmin / tmax are per-ray CUDA float32 tensors (the
+        form Ray3C carries, src/ray.h:20-26) or scalars"""
+        import torch
+        n = origin[0].numel()
+        rs = RayStreams(*[t_.data_ptr() for t_ in list(origin) + list(direction)], None, None, 0.0, 0.0)
+        for name, val in (("tmin", tmin), ("tmax", tmax)):
+            if torch.is_tensor(val):
+                assert val.is_cuda and val.dtype == torch.float32 and val.is_contiguous() and val.numel() == n
+                setattr(rs, name, val.data_ptr())
+            else:
+                setattr(rs, name + "_scalar", float(val))
+        return rs
+
+    def hit_attributes(self, origin, direction, hit, want=("p", "gn", "sn", "uv", "mat"), stream=None):
+        """The derived attributes OptixBackend::intersect returns with a hit (src/accel/optix_backend.h:463-486) and
+        the material index of Scene::intersect (src/main.cpp:325).  origin / direction: the ray streams; hit: the
+        (tri_id, t, u, v) tensors of intersect().  Returns a dict of CUDA tensors: p [3][n], gn [3][n], sn [3][n],
+        uv [2][n], mat [n]; lanes that missed keep NaN / -1."""
+        import torch
+        n = hit[0].numel()
+        dev = hit[0].device
+        out, hs = {}, HitAttrStreams()
+        for key, names in (("p", ("px", "py", "pz")), ("gn", ("gnx", "gny", "gnz")), ("sn", ("snx", "sny", "snz")),
+                           ("uv", ("tu", "tv"))):
+            if key in want:
+                out[key] = torch.full((len(names), n), float("nan"), dtype=torch.float32, device=dev)
+                for k, nm in enumerate(names):
+                    setattr(hs, nm, out[key][k].data_ptr())
+        if "mat" in want:
+            out["mat"] = torch.full((n,), -1, dtype=torch.int32, device=dev)
+            hs.material_id = out["mat"].data_ptr()
+        rs = self._ray_streams(origin, direction)
+        h = HitStreams(*[t_.data_ptr() for t_ in hit])
+        _check(lib().wpt_hit_attributes(self._h, C.byref(rs), C.byref(h), C.c_uint32(n), C.byref(hs), _stream_handle(stream)))
         return out
 
     def intersect_host(self, o, d, active=None, tmin=1e-3, tmax=1e20):
@@ -330,6 +402,10 @@ class Renderer:
         """True / False, or an int > 1 = seed margin in 1/10000 (tests)"""
         _check(lib().wpt_renderer_set_depth_seeding(self._h, C.c_int(int(on))))
 
+    def set_tail(self, first_bounce=0):
+        """bounces >= first_bounce run in one fused trace+shade launch per pass; 0 = default, negative = off"""
+        _check(lib().wpt_renderer_set_tail(self._h, C.c_int(int(first_bounce))))
+
     def set_tuning(self, trace_variant=0, ctas_per_sm=0, overlap_lanes=0):
         _check(lib().wpt_renderer_set_tuning(self._h, C.c_int(trace_variant), C.c_int(ctas_per_sm), C.c_int(overlap_lanes)))
 
@@ -353,12 +429,17 @@ class Renderer:
     def render_host(self, camera, spp_begin, spp_count, depth, seed=0, tmin=1e-3, tmax=1e20, out=None):
         """whole frame to HOST planar film [3, H*W], normalised by spp_count (src/main.cpp:369-439)."""
         N = self.width * self.height
-        film = out if out is not None else np.empty((3, N), np.float32)
+        if out is None:
+            # the renderer's own pinned film (wpt_host_alloc): the D2H copies are plain DMA transfers
+            if getattr(self, "_pinned", None) is None:
+                self._pinned = PinnedArray((3, N))
+            out = self._pinned.array
+        film = out
         cfg = self._cfg(spp_begin, spp_count, depth, seed, tmin, tmax)
         st = Stats()
         _check(lib().wpt_render_host(self._h, C.byref(camera.c), C.byref(cfg), C.c_void_p(film[0].ctypes.data),
                                      C.c_void_p(film[1].ctypes.data), C.c_void_p(film[2].ctypes.data), C.byref(st)))
-        return film, _stats_dict(st)
+        return (film if film is not getattr(getattr(self, "_pinned", None), "array", None) else film.copy()), _stats_dict(st)
 
     def close(self):
         if self._h:

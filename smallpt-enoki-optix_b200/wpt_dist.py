@@ -1,8 +1,10 @@
 """Multi-GPU plumbing: samples-per-pixel shard across ranks, one rank per GPU.
 Work unit = (pixel, global spp index); paths never interact and the film is a sum, so the only
 exchange step is ONE reduce of the partial films (3*W*H floats) onto rank 0.  The scene/BVH is
-replicated.  torch.distributed is plumbing: NCCL over NVLink on the GPU box, gloo in the CPU tests.
-The reference has no counterpart (single process, single GPU)."""
+replicated.  On the GPU box the reduce is wpt_film_reduce of the C ABI (libwpt.so -> ncclReduce over NVLink, its own
+communicator); torch.distributed only ships the 128-byte NCCL id at start-up (FilmReducer) and runs the gloo reduce of
+the CPU tests.  The reference has no counterpart (single process, single GPU)."""
+import ctypes as C
 
 
 def spp_range_strong(rank, world, spp_total):
@@ -31,3 +33,40 @@ def reduce_film(film, dst=0):
         return 1
     dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
     return dist.get_world_size()
+
+
+class FilmReducer:
+    """One NCCL communicator owned by libwpt.so (wpt_nccl_comm_create) + wpt_film_reduce on it.  The rendezvous —
+    rank 0's ncclUniqueId to every rank — goes through an already initialised torch.distributed group (any backend);
+    the data plane does not: the reduce is enqueued by libwpt on the caller's CUDA stream."""
+
+    def __init__(self, device):
+        import torch
+        import torch.distributed as dist
+        import wpt
+        self.L = wpt.lib()
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        idb = (C.c_char * 128)()
+        if self.rank == 0:
+            wpt._check(self.L.wpt_nccl_unique_id(idb))
+        t = torch.frombuffer(bytearray(idb.raw), dtype=torch.uint8).clone()
+        if dist.get_backend() == "nccl":
+            t = t.cuda(device)
+        dist.broadcast(t, src=0)
+        raw = bytes(t.cpu().numpy().tobytes())
+        self.comm = C.c_void_p()
+        wpt._check(self.L.wpt_nccl_comm_create(C.c_char_p(raw), C.c_int(self.world), C.c_int(self.rank), C.c_int(device),
+                                               C.byref(self.comm)))
+
+    def reduce(self, film, root=0, stream=None):
+        """film: CUDA float32 [3, N] planar; summed in place onto `root`, asynchronously on `stream`"""
+        import wpt
+        N = film.numel() // 3
+        base = film.data_ptr()
+        wpt._check(self.L.wpt_film_reduce(self.comm, C.c_void_p(base), C.c_void_p(base + 4 * N), C.c_void_p(base + 8 * N),
+                                          C.c_uint32(N), C.c_int(root), wpt._stream_handle(stream)))
+
+    def close(self):
+        if self.comm:
+            self.L.wpt_nccl_comm_destroy(self.comm)
+            self.comm = C.c_void_p()

@@ -47,4 +47,5 @@ def built():
 @pytest.fixture(scope="session")
 def hosttest():
     import ctypes as C
-    return C.CDLL(os.path.join(PKG, "libwpt_hosttest.so"))
+    # WPT_HOSTTEST_LIB: tools/sanitize.sh points this at the ASan/UBSan build
+    return C.CDLL(os.environ.get("WPT_HOSTTEST_LIB", os.path.join(PKG, "libwpt_hosttest.so")))

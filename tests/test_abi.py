@@ -23,7 +23,7 @@ def test_exports_match_header():
     assert len(names) >= 20
     for n in names:
         assert hasattr(L, n), f"libwpt.so does not export {n}"
-    assert L.wpt_version() == 100
+    assert L.wpt_version() == 200
 
 
 def test_host_only_entry_points(tmp_path):

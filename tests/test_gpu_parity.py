@@ -74,7 +74,8 @@ def test_intersect_vs_oracle_cornell(torch_cuda, cornell, inside):
     rate = util.compare_hits(ref, got, "cornell/oracle")
     assert rate >= 0.9999
     if O.ref_available():
-        util.compare_hits(om.intersect("embree", o, d), got, "cornell/embree")
+        fast, robust = util.embree_pair(om, o, d)
+        util.compare_hits(fast, got, "cornell/embree", robust=robust)
 
 
 def test_intersect_mask_semantics(torch_cuda, cornell):
@@ -129,8 +130,8 @@ def test_intersect_knob_camera_and_bounce_rays(torch_cuda):
     o = np.stack([x.cpu().numpy() for x in o_t], 1)
     d = np.stack([x.cpu().numpy() for x in d_t], 1)
     got = tuple(x.cpu().numpy() for x in hit)
-    ref = om.intersect("embree" if O.ref_available() else "bvh", o, d)
-    assert util.compare_hits(ref, got, "knob/camera") >= 0.9999
+    ref, robust = util.embree_pair(om, o, d)
+    assert util.compare_hits(ref, got, "knob/camera", robust=robust) >= 0.9999
     # bounce rays from the hit points
     live = got[0] >= 0
     n = int(live.sum())
@@ -145,8 +146,8 @@ def test_intersect_knob_camera_and_bounce_rays(torch_cuda):
     o2 = np.stack([x.cpu().numpy() for x in no], 1)
     d2 = np.stack([x.cpu().numpy() for x in nd], 1)
     got2 = tuple(x.cpu().numpy() for x in hit2)
-    ref2 = om.intersect("embree" if O.ref_available() else "bvh", o2, d2)
-    assert util.compare_hits(ref2, got2, "knob/bounce") >= 0.9999
+    ref2, robust2 = util.embree_pair(om, o2, d2)
+    assert util.compare_hits(ref2, got2, "knob/bounce", robust=robust2) >= 0.9999
 
 
 def test_philox_kat(torch_cuda):
@@ -240,8 +241,8 @@ def test_render_three_sigma_vs_reference_rng(torch_cuda):
     sd = scenes.cornell(50)
     spp = 64
     film, st, ofilm, oseg = _render_both(sd, 96, 96, spp, 5, seed=77, rng_mode=O.RNG_PCG32, spp_per_pass=8)
-    frac = util.three_sigma_outliers(film[0], ofilm[0], spp)
-    assert frac < 0.01, f"{frac} of pixels outside 3 sigma"
+    frac, z2 = util.three_sigma_outliers(film, ofilm, spp)           # all three channels
+    assert frac < 0.005 and z2 < 1.15, f"{frac} of pixel values outside 3 sigma, mean z^2 {z2}"
     assert abs(film.mean() - ofilm.mean()) < 0.01 * ofilm.mean()
     assert abs(st["segments"] - oseg) < 0.01 * oseg
 
@@ -278,7 +279,7 @@ def test_trace_variants_agree(torch_cuda):
     cam = wpt.camera_from(sd)
     W = H = 64
     films = []
-    for variant in (0, 1, 2, 5, 12):   # 12: two shared stack rows, local-memory overflow exercised
+    for variant in (0, 1, 2, 12, 20, 21, 22, 23):   # 12: two shared stack rows, local-memory overflow exercised; 20: per-entry flush
         r = wpt.Renderer(scene, W, H, 2)
         r.set_tuning(trace_variant=variant)
         f = torch.zeros(3, W * H, device="cuda")
@@ -548,10 +549,10 @@ def test_depth_seeding_is_exact(torch_cuda):
         # not seeded: fewer than 8 samples, or a thin lens
         r = wpt.Renderer(scene, W, H, 4)
         r.render(cam, torch.zeros(3, W * H, device="cuda"), 0, 4, 3, seed=1)
-        assert r.finish()["kernel_launches"] == 1 + 2 * 3
+        assert r.finish()["kernel_launches"] == 1 + 2 * 2 + 1      # raygen, two wavefront bounces, the fused tail
         c = sd.camera
         lens = wpt.ThinlensCamera(c["look_from"], c["look_at"], c["up"], 0.05, 3.0, c["fov_y"])
         r.render(lens, torch.zeros(3, W * H, device="cuda"), 0, 8, 2, seed=1)
         st = r.finish()
-        assert st["kernel_launches"] == 2 * (1 + 2 * 2) and st["retraced"] == 0
+        assert st["kernel_launches"] == 2 * (1 + 2 * 2) and st["retraced"] == 0      # depth 2: no tail
         r.close()

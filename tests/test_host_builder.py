@@ -158,3 +158,13 @@ def test_stack_never_exceeds_tree_depth_minus_one(hosttest):
         assert max_depth >= 3 and 1 <= stack_hi <= max_depth - 1, (stack_hi, max_depth)
         if sd.name == "spiral":   # 17 levels: the launcher takes the kernel with the local-memory overflow
             assert max_depth > 15 and stack_hi >= 5, (stack_hi, max_depth)
+
+
+def test_block_count_limit(hosttest):
+    """the warp queue packs (owner lane << 27 | block index); wpt_scene_commit refuses trees with more than
+    2^27 blocks (WPT_E_LIMIT) instead of silently corrupting the owner lane"""
+    import ctypes as C
+    f = hosttest.wpt_hosttest_blocks_within_limit
+    f.argtypes = [C.c_uint64]
+    assert f(1) == 1 and f((1 << 27) - 1) == 1 and f(1 << 27) == 1
+    assert f((1 << 27) + 1) == 0 and f(1 << 31) == 0 and f(715_000_000) == 0

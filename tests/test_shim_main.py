@@ -55,3 +55,83 @@ def test_main_writes_the_same_image_as_the_python_mirror(tmp_path):
     # same kernels, same counters; film accumulation order (float atomics) is the only freedom
     assert np.allclose(img, film, rtol=0, atol=2e-6)
     assert img.max() > 0
+
+
+def test_shim_frame3_matches_the_oracle():
+    """Frame3 of the shim (src/coordframe.h:5-54, host scalar form) against the oracle's restatement: same matrix,
+    to_world / to_local bit for bit"""
+    import ctypes as C
+    import oracle_py as O
+    src = os.path.join(ROOT, "tests", "_frame3_probe.cpp")
+    exe = os.path.join(PKG, "build", "frame3_probe")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    open(src, "w").write('#include <cstdio>\n#include <cstdlib>\n#include "wpt_shim.hpp"\nint main(int c, char **v){ using namespace wpt_shim;'
+                         ' Real3 n(atof(v[1]),atof(v[2]),atof(v[3])), x(atof(v[4]),atof(v[5]),atof(v[6])); Frame3 f(n);'
+                         ' Real3 w=f.to_world(x), l=f.to_local(x); for(int k=0;k<9;k++) printf("%a ",f.m_world_from_local[k]);'
+                         ' printf("%a %a %a %a %a %a\\n",w.x,w.y,w.z,l.x,l.y,l.z); return 0; }\n')
+    try:
+        subprocess.run(["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"), "-o", exe, src,
+                        "-L", PKG, "-lwpt", f"-Wl,-rpath,{PKG}"], check=True)
+    finally:
+        os.remove(src)
+    L = O.lib()
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        n = rng.normal(size=3).astype(np.float32); n /= np.linalg.norm(n)
+        x = rng.normal(size=3).astype(np.float32)
+        out = subprocess.run([exe] + [float(a).hex() for a in n] + [float(a).hex() for a in x], capture_output=True, text=True).stdout.split()
+        got = np.array([float.fromhex(t) for t in out], np.float32)
+        m = (C.c_float * 9)(); w = (C.c_float * 3)(); l = (C.c_float * 3)()
+        L.orc_frame_from_normal((C.c_float * 3)(*n), m)
+        L.orc_frame_to_world(m, (C.c_float * 3)(*x), w)
+        L.orc_frame_to_local(m, (C.c_float * 3)(*x), l)
+        assert np.array_equal(got[:9], np.array(m, np.float32))
+        assert np.array_equal(got[9:12], np.array(w, np.float32)) and np.array_equal(got[12:], np.array(l, np.float32))
+
+
+@pytest.mark.gpu
+def test_main_sharded_over_two_gpus_writes_the_same_image(tmp_path):
+    """wurst --gpus 2: ShardedPathLoop (spp shards + ONE wpt_film_reduce, no Python) == the single-GPU image"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run under gpurun --gpus 2)")
+    a, b = tmp_path / "one.pfm", tmp_path / "two.pfm"
+    for out, extra in ((a, []), (b, ["--gpus", "2"])):
+        r = subprocess.run([WURST, OBJ, str(out), "64", "48", "8", "3", "--kd"] + extra, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    assert np.allclose(_read_pfm(a), _read_pfm(b), rtol=0, atol=2e-6)
+
+
+@pytest.mark.gpu
+def test_shim_scene_intersect_returns_the_interaction(tmp_path):
+    """Scene::intersect of the shim fills an Interaction (src/main.cpp:255-284, 320-340): hit record, position,
+    normals, texcoord and material per lane — checked against the Python mirror on the same rays"""
+    src = tmp_path / "t.cpp"
+    src.write_text('''#include <cstdio>
+#include "wpt_shim.hpp"
+using namespace wpt_shim;
+int main(int, char **v) {
+    Scene sc; sc.add_triangle_mesh(v[1], true); sc.commit();
+    const uint32_t n = 4096;
+    std::vector<float> o[3], d[3];
+    for (uint32_t i = 0; i < n; i++) { o[0].push_back(-0.9f + 1.8f * (i % 64) / 63.f); o[1].push_back(0.1f + 1.8f * (i / 64) / 63.f); o[2].push_back(4.f);
+                                       d[0].push_back(0.f); d[1].push_back(0.f); d[2].push_back(-1.f); }
+    RealC ox = RealC::copy(o[0].data(), n), oy = RealC::copy(o[1].data(), n), oz = RealC::copy(o[2].data(), n);
+    RealC dx = RealC::copy(d[0].data(), n), dy = RealC::copy(d[1].data(), n), dz = RealC::copy(d[2].data(), n);
+    Ray3C ray{ox.data(), oy.data(), oz.data(), dx.data(), dy.data(), dz.data(), n};
+    Interaction it(n);
+    sc.intersect(ray, nullptr, 0, it);
+    auto id = it.m_hit.m_tri_id.to_host(); auto pz = it.m_hit.m_position[2].to_host(); auto gz = it.m_hit.m_geometry_normal[2].to_host();
+    auto mat = it.m_scatter.to_host(); auto t = it.m_hit.m_t.to_host();
+    int hits = 0; double err = 0;
+    for (uint32_t i = 0; i < n; i++) if (id[i] >= 0) { hits++; err += std::fabs(pz[i] - (4.f - t[i])) + (mat[i] < 0) + (std::fabs(std::fabs(gz[i]) - 1.f) > 1e-5f && std::fabs(gz[i]) > 1e-5f); }
+    std::printf("%d %g\\n", hits, err);
+    return 0; }
+''')
+    exe = tmp_path / "t"
+    subprocess.run(["g++", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src), "-L", PKG, "-lwpt",
+                    f"-Wl,-rpath,{PKG}"], check=True)
+    r = subprocess.run([str(exe), OBJ], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    hits, err = r.stdout.split()
+    assert int(hits) > 1000 and float(err) < 1e-3
