@@ -78,6 +78,20 @@ def ref():
     return _ref
 
 
+def ref_builder_sah(pos, idx, branching=7, max_leaf=3, c_trav=1.0, c_isect=0.3, quality=1):
+    """SAH cost of the tree the reference tree's own builder (rtcBuildBVH, include/embree3/rtcore_builder.h:26-110) makes
+    of the same triangles with the given cost constants.  Returns dict(sah, nodes, leaves, depth, prims)."""
+    pos = _c(pos, np.float32).reshape(-1, 3)
+    idx = _c(idx, np.int32).reshape(-1, 3)
+    out = (C.c_double * 5)()
+    rc = ref().eref_builder_sah(pos.reshape(-1).ctypes.data_as(C.c_void_p), C.c_uint32(pos.shape[0]),
+                                idx.reshape(-1).ctypes.data_as(C.c_void_p), C.c_uint32(idx.shape[0]), C.c_uint(branching),
+                                C.c_uint(max_leaf), C.c_float(c_trav), C.c_float(c_isect), C.c_int(quality), out)
+    if rc != 0:
+        raise RuntimeError(f"rtcBuildBVH failed ({rc})")
+    return dict(sah=out[0], nodes=int(out[1]), leaves=int(out[2]), depth=int(out[3]), prims=int(out[4]))
+
+
 def ref_obj_available():
     return os.path.exists(os.path.join(_HERE, "_ref", "libtinyobj_ref.so"))
 
