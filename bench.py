@@ -236,6 +236,8 @@ def run_ours(args):
     r.set_tuning(args.variant, args.ctas_per_sm, args.overlap)
     r.set_depth_seeding(args.seeding)
     r.set_tail(args.tail)
+    if reducer is not None and args.depth_shard:
+        r.set_depth_shard(reducer.comm, rank, world)            # 1/N of the depth pre-pass per rank + one all-gather
     film = torch.zeros(3, N, device="cuda")
 
     def step():
@@ -360,8 +362,7 @@ def run_ours(args):
         r.set_profile(False)
         ab = alg_bytes(sd.n_tris)
         peak, which = measured_peak_gbs()
-        tail = args.tail if args.tail != 0 else 2
-        wave = tail if 1 <= tail < depth else depth
+        wave = pst["tail_from"] if pst["tail_from"] >= 1 else depth
         n_trace = pst["passes"] * (wave + (1 if wave < depth else 0))
         if args.seeding and spp >= 8 and cam.c.lens_radius == 0.0:
             n_trace += 1 + pst["passes"]      # depth pre-pass + one second-trace launch per pass (wpt_render)
@@ -408,7 +409,8 @@ def run_ours(args):
                            "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass,
                            "parallelism": f"spp-shard x{world}", "reduce": "wpt_film_reduce (ncclReduce, own communicator)" if world > 1 else None,
                            "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph), "depth_seeding": int(args.seeding),
-                           "fused_tail_from": args.tail if args.tail != 0 else 2, "trace_variant": args.variant,
+                           "fused_tail_from": st["tail_from"], "trace_variant": args.variant,
+                           "depth_prepass_sharded": bool(reducer is not None and args.depth_shard),
                            "l2": "inputs larger than L2: ray/hit queues %.0f MB per pass + %.0f MB BVH" % (
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
@@ -437,7 +439,8 @@ def main():
     ap.add_argument("--overlap", type=int, default=1, help="1 = two lanes on two streams (shade of one overlaps trace of the other)")
     ap.add_argument("--scaling", choices=("weak", "strong"), default="strong",
                     help="strong (default): the frame's --spp samples split over the ranks; weak: every rank renders --spp samples")
-    ap.add_argument("--tail", type=int, default=0, help="fused tail from this bounce on (0 = default, -1 = off)")
+    ap.add_argument("--tail", type=int, default=0, help="fused tail from this bounce on (0 = automatic, -1 = off)")
+    ap.add_argument("--depth-shard", type=int, default=1, help="N>1: 1 = shard the depth pre-pass over the ranks (default)")
     ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
     ap.add_argument("--seeding", type=int, default=1, help="1 = depth seeding of the camera rays (default), 0 = off")
     ap.add_argument("--no-cpu", action="store_true")

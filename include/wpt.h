@@ -68,6 +68,12 @@ int  wpt_scene_create(const wpt_mesh_desc *mesh, wpt_scene **out);
 /* Optional texture coordinates (src/main.cpp:215-223: texcoords f32[2*n_uvs], texcoord_triplets i32[3*n_triangles],
  * -1 = none): only wpt_hit_attributes reads them.  Call before wpt_scene_commit. */
 int  wpt_scene_set_texcoords(wpt_scene *s, const float *uvs, const int32_t *uv_triplets, uint32_t n_uvs);
+/* Image texture of one material: rgb f32[3*width*height], texel (x, y) at y*width + x.  The bsdf weight of that
+ * material becomes ImageTexture::eval (src/main.cpp:62-76) at the hit's interpolated texcoord (wpt_scene_set_texcoords):
+ * bilinear, clamped, same operation order as the reference.  Its texel_fetch indexes y * size.y + x (src/main.cpp:52),
+ * wrong for non-square images; this library (and the oracle) use the row length, y * size.x + x.  A 1x1 texture is the
+ * constant albedo the reference builds for every material (src/main.cpp:40-44,104-106).  Call before wpt_scene_commit. */
+int  wpt_scene_set_texture(wpt_scene *s, uint32_t material, const float *rgb, uint32_t width, uint32_t height);
 /* SAH BVH build on the host, flatten to 64-byte 7-wide quantised nodes + 64-byte triangle blocks (one buffer),
  * one upload to `device`.  WPT_E_LIMIT if the tree is deeper than 32 levels or holds more than 2^27 blocks
  * (nodes + triangles; about 115 M triangles).  If the vertices were last moved by wpt_scene_refit_device, a
@@ -183,6 +189,8 @@ typedef struct {
     uint32_t passes, kernel_launches;
     float    ms_total, ms_raygen, ms_trace, ms_shade; /* CUDA-event times; per-kernel only if profile=1 */
     uint64_t retraced;                    /* depth-seeded camera rays that had to be traced a second time (not in segments) */
+    int32_t  tail_from;                   /* first bounce the fused tail kernel covered in this render, -1 = none */
+    int32_t  reserved;
 } wpt_stats;
 
 typedef struct wpt_renderer wpt_renderer;
@@ -198,11 +206,18 @@ int  wpt_renderer_set_profile(wpt_renderer *r, int profile);
  * counters and film are those of the unseeded render.  on = 0 switches it off; on > 1 sets the margin to on/10000
  * (a margin below 1 makes most seeds too short: only useful to exercise the second trace). */
 int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
+/* Sharded depth pre-pass for a frame split over n_ranks GPUs (wpt_film_reduce below): every rank needs the same seeds,
+ * so instead of all of them repeating the whole one-ray-per-pixel pre-pass, rank g traces 1/n_ranks of it and the hit
+ * distances are all-gathered on `nccl_comm` (ncclAllGather, W*H floats in total) inside wpt_render, on its stream.
+ * EVERY rank of the communicator must then call wpt_render for every frame (it is a collective).  The seeds, hence
+ * the frame, are bit-identical to the unsharded pre-pass.  nccl_comm = NULL or n_ranks <= 1 switches it off. */
+int  wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, int rank, int n_ranks);
 /* Fused tail: bounces >= first_bounce of every pass run in ONE launch of the traversal kernel with the shading step
  * fused in (a path whose segment ends is shaded by its own lane and continues in place) instead of one trace + one
  * shade launch per bounce — late bounces hold few paths and a persistent launch has a fixed ramp-up/drain cost.
- * Same Philox counters, same paths, same film up to fp32 atomic order.  first_bounce >= 1; 0 = default (2);
- * negative = off (a wavefront launch pair for every bounce). */
+ * Same Philox counters, same paths, same film up to fp32 atomic order.  first_bounce >= 1; negative = off (a wavefront
+ * launch pair for every bounce); 0 = automatic (default): from bounce 2 on when a pass holds at most 2^25 paths, off
+ * for larger passes, where it does not pay (profiles/r2_grid_c3.txt). */
 int  wpt_renderer_set_tail(wpt_renderer *r, int first_bounce);
 /* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders
  * alternate passes on two internal streams (each lane holds half of spp_per_pass in its own queues) so that

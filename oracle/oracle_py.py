@@ -14,7 +14,12 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 class OrcMesh(C.Structure):
     _fields_ = [("pos", C.c_void_p), ("pos_idx", C.c_void_p), ("nrm", C.c_void_p), ("nrm_idx", C.c_void_p),
                 ("mat_id", C.c_void_p), ("albedo", C.c_void_p),
-                ("n_tris", C.c_uint32), ("n_pos", C.c_uint32), ("n_nrm", C.c_uint32), ("n_mat", C.c_uint32)]
+                ("n_tris", C.c_uint32), ("n_pos", C.c_uint32), ("n_nrm", C.c_uint32), ("n_mat", C.c_uint32),
+                ("uvs", C.c_void_p), ("uv_idx", C.c_void_p), ("tex", C.c_void_p)]
+
+
+class OrcTexture(C.Structure):
+    _fields_ = [("rgb", C.c_void_p), ("w", C.c_int32), ("h", C.c_int32)]
 
 
 class OrcCamera(C.Structure):
@@ -140,6 +145,21 @@ class Mesh:
                          T, self.pos.shape[0], self.nrm.shape[0], self.albedo.shape[0])
         self._bvh = None
         self._eref = None
+
+    def set_textures(self, uvs, uv_idx, textures):
+        """textures: dict material -> float32 array (h, w, 3); uvs (n,2), uv_idx (T,3) with -1 = none"""
+        self._uvs = _c(uvs, np.float32).reshape(-1, 2)
+        self._uvidx = _c(uv_idx, np.int32).reshape(-1, 3)
+        n_mat = self.albedo.shape[0]
+        self._tex_arr = (OrcTexture * n_mat)()
+        self._tex_keep = {}
+        for m, img in textures.items():
+            img = _c(img, np.float32)
+            self._tex_keep[m] = img
+            self._tex_arr[m] = OrcTexture(img.ctypes.data, img.shape[1], img.shape[0])
+        self.c.uvs = self._uvs.ctypes.data
+        self.c.uv_idx = self._uvidx.ctypes.data
+        self.c.tex = C.cast(self._tex_arr, C.c_void_p).value
 
     @property
     def n_tris(self):

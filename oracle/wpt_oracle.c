@@ -454,6 +454,24 @@ void orc_intersect_streams_win(orc_intersect1_fn fn, void *ctx,
     }
 }
 
+/* ImageTexture::eval, src/main.cpp:62-76 (texel_fetch_wrap :56-60 clamps; index bug of :52 fixed) */
+void orc_texture_eval(const orc_texture *t, float u, float v, float rgb[3])
+{
+    const float su = u * (float)t->w - 0.5f, sv = v * (float)t->h - 0.5f;
+    const float fx = floorf(su), fy = floorf(sv);
+    const int x = (int)fx, y = (int)fy;
+    const float dx1 = su - fx, dy1 = sv - fy, dx2 = 1.0f - dx1, dy2 = 1.0f - dy1;
+    const int W = t->w, H = t->h;
+#define CL(a, n) ((a) < 0 ? 0 : ((a) > (n) - 1 ? (n) - 1 : (a)))
+    const int x0 = CL(x, W), x1 = CL(x + 1, W), y0 = CL(y, H), y1 = CL(y + 1, H);
+#undef CL
+    for (int k = 0; k < 3; k++) {
+        const float t00 = t->rgb[3 * (y0 * W + x0) + k], t01 = t->rgb[3 * (y1 * W + x0) + k];
+        const float t10 = t->rgb[3 * (y0 * W + x1) + k], t11 = t->rgb[3 * (y1 * W + x1) + k];
+        rgb[k] = t00 * dx2 * dy2 + t01 * dx2 * dy1 + t10 * dx1 * dy2 + t11 * dx1 * dy1;
+    }
+}
+
 /* ------------------------------------------------------------------ shading step
  * optix_backend.h:469 (p = o + t d), :483-484 (interpolated, un-normalised shading normal),
  * main.cpp:325-326 (material), :414-424 (frame, Lambert sample, next ray). */
@@ -485,6 +503,19 @@ void orc_shade_step(const orc_mesh *m, const float o[3], const float d[3], int32
     orc_frame_to_world(fr, local, next_d);
     const int32_t mat = m->mat_id ? m->mat_id[tri] : 0;
     for (int k = 0; k < 3; k++) weight[k] = m->albedo ? m->albedo[3 * mat + k] : 1.0f;
+    if (m->tex && m->tex[mat].rgb && m->tex[mat].w * m->tex[mat].h > 1) {
+        /* LambertBsdf::sample -> m_reflectance->eval(texcoord) (main.cpp:116) at the interpolated texcoord
+         * (optix_backend.h:479-480); faces without texcoords evaluate at (0,0) */
+        float tu = 0.0f, tv = 0.0f;
+        if (m->uvs && m->uv_idx && m->uv_idx[3 * tri] >= 0 && m->uv_idx[3 * tri + 1] >= 0 && m->uv_idx[3 * tri + 2] >= 0) {
+            const float w = 1.0f - u - v;
+            const float *a = m->uvs + 2 * (size_t)m->uv_idx[3 * tri], *b = m->uvs + 2 * (size_t)m->uv_idx[3 * tri + 1],
+                        *c = m->uvs + 2 * (size_t)m->uv_idx[3 * tri + 2];
+            tu = w * a[0] + u * b[0] + v * c[0];
+            tv = w * a[1] + u * b[1] + v * c[1];
+        }
+        orc_texture_eval(&m->tex[mat], tu, tv, weight);
+    }
 }
 
 /* optix_backend.h:463-486 + main.cpp:325; faces without normals: the documented deviation of orc_shade_step */

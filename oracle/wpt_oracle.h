@@ -76,7 +76,16 @@ typedef struct {
     const int32_t *mat_id;   /* n_tris */
     const float   *albedo;   /* 3*n_mat */
     uint32_t n_tris, n_pos, n_nrm, n_mat;
+    /* optional (may all be NULL): texture coordinates (main.cpp:215-223) and one ImageTexture per material
+     * (main.cpp:35-80); a material whose texture is NULL / 1x1 uses its constant albedo */
+    const float   *uvs;      /* 2*n_uv */
+    const int32_t *uv_idx;   /* 3*n_tris, -1 = none */
+    const struct orc_texture *tex;   /* n_mat entries */
 } orc_mesh;
+typedef struct orc_texture { const float *rgb; int32_t w, h; } orc_texture;
+/* ImageTexture::eval (src/main.cpp:62-76): bilinear, clamped; texel (x,y) at y*w + x (the reference's :52 uses
+ * y*size.y + x, a bug for non-square images, fixed here and in the product) */
+void orc_texture_eval(const orc_texture *t, float u, float v, float rgb[3]);
 
 /* single ray / single triangle, Embree accept rules; on accept updates *tfar,*u,*v, returns 1 */
 int orc_tri_intersect(const float o[3], const float d[3], float tnear, float *tfar,

@@ -17,6 +17,7 @@
 #include "bvh_build.h"
 #include "kernels.cuh"
 #include "obj_load.h"
+#include "shade_core.h"   // MatTex
 
 using namespace wpt;
 
@@ -49,6 +50,13 @@ struct wpt_scene {
     std::vector<float> pos, nrm, albedo, uvs;
     std::vector<int32_t> pidx, nidx, mat, uvidx;
     uint32_t n_tris = 0;
+    // image textures per material (wpt_scene_set_texture): rgb f32[3*w*h]; none = the constant albedo
+    std::vector<std::vector<float>> tex_rgb;
+    std::vector<uint32_t> tex_w, tex_h;
+    float4 *d_texels = nullptr;
+    MatTex *d_mattex = nullptr;
+    float2 *d_triuv = nullptr;
+    TexArgs tex{nullptr, nullptr, nullptr};
     bool pos_on_device_newer = false;   // wpt_scene_refit_device moved the vertices: the next commit reads them back
     // device
     int device = -1, num_sms = 0;
@@ -108,8 +116,9 @@ static void scene_free_device(wpt_scene *s)
     cudaFree(s->d_blocks); cudaFree(s->d_attr);
     cudaFree(s->d_albedo); cudaFree(s->d_cursor);
     cudaFree(s->d_level_nodes); cudaFree(s->d_geo); cudaFree(s->d_pos); cudaFree(s->d_boxes); cudaFree(s->d_pidx);
-    cudaFree(s->d_uvs); cudaFree(s->d_uvidx);
-    s->d_uvs = nullptr; s->d_uvidx = nullptr;
+    cudaFree(s->d_uvs); cudaFree(s->d_uvidx); cudaFree(s->d_texels); cudaFree(s->d_mattex); cudaFree(s->d_triuv);
+    s->d_uvs = nullptr; s->d_uvidx = nullptr; s->d_texels = nullptr; s->d_mattex = nullptr; s->d_triuv = nullptr;
+    s->tex = TexArgs{nullptr, nullptr, nullptr};
     s->d_blocks = nullptr; s->d_attr = nullptr;
     s->d_albedo = nullptr; s->d_cursor = nullptr;
     s->d_level_nodes = nullptr; s->d_geo = nullptr; s->d_pos = nullptr; s->d_boxes = nullptr; s->d_pidx = nullptr;
@@ -209,6 +218,35 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
         WPT_CUDA(cudaMalloc(&s->d_uvidx, s->uvidx.size() * sizeof(int32_t)));
         WPT_CUDA(cudaMemcpy(s->d_uvs, s->uvs.data(), s->uvs.size() * sizeof(float), cudaMemcpyHostToDevice));
         WPT_CUDA(cudaMemcpy(s->d_uvidx, s->uvidx.data(), s->uvidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    // image textures: one float4 texel pool, a window per material, three texcoords per original triangle
+    bool any_tex = false;
+    for (size_t m = 0; m < s->tex_rgb.size(); m++) any_tex = any_tex || (s->tex_w[m] * s->tex_h[m] > 1u);
+    if (any_tex) {
+        const size_t n_mat = s->albedo.size() / 3;
+        std::vector<MatTex> mt(n_mat, MatTex{0u, 1u, 1u, 0u});
+        std::vector<float4> texels;
+        for (size_t m = 0; m < n_mat && m < s->tex_rgb.size(); m++) {
+            if (s->tex_w[m] * s->tex_h[m] <= 1u) continue;
+            mt[m] = MatTex{(uint32_t)texels.size(), s->tex_w[m], s->tex_h[m], 0u};
+            for (size_t k = 0; k < (size_t)s->tex_w[m] * s->tex_h[m]; k++)
+                texels.push_back(make_float4(s->tex_rgb[m][3 * k], s->tex_rgb[m][3 * k + 1], s->tex_rgb[m][3 * k + 2], 0.0f));
+        }
+        std::vector<float2> triuv(3 * (size_t)s->n_tris, make_float2(0.0f, 0.0f));
+        if (!s->uvs.empty())
+            for (size_t k = 0; k < 3 * (size_t)s->n_tris; k++) {
+                // a face without texcoords (any index < 0) evaluates at (0, 0) in all three corners
+                const size_t f = k / 3;
+                const bool ok = s->uvidx[3 * f] >= 0 && s->uvidx[3 * f + 1] >= 0 && s->uvidx[3 * f + 2] >= 0;
+                if (ok) triuv[k] = make_float2(s->uvs[2 * (size_t)s->uvidx[k]], s->uvs[2 * (size_t)s->uvidx[k] + 1]);
+            }
+        WPT_CUDA(cudaMalloc(&s->d_texels, texels.size() * sizeof(float4)));
+        WPT_CUDA(cudaMalloc(&s->d_mattex, mt.size() * sizeof(MatTex)));
+        WPT_CUDA(cudaMalloc(&s->d_triuv, triuv.size() * sizeof(float2)));
+        WPT_CUDA(cudaMemcpy(s->d_texels, texels.data(), texels.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        WPT_CUDA(cudaMemcpy(s->d_mattex, mt.data(), mt.size() * sizeof(MatTex), cudaMemcpyHostToDevice));
+        WPT_CUDA(cudaMemcpy(s->d_triuv, triuv.data(), triuv.size() * sizeof(float2), cudaMemcpyHostToDevice));
+        s->tex = TexArgs{s->d_texels, s->d_mattex, s->d_triuv};
     }
     WPT_CUDA(cudaDeviceSynchronize());
     const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
@@ -460,7 +498,55 @@ extern "C" int wpt_camera_init(wpt_camera *c, const float from[3], const float a
 // ------------------------------------------------------------------------------------------------
 // renderer: the sample/bounce loop (src/main.cpp:385-426) as a wavefront pipeline
 // ------------------------------------------------------------------------------------------------
-constexpr int kDefaultTailFrom = 2;   // measured on C3 (profiles/r2_*); <= 0 = no fused tail
+// ---- NCCL, bound at run time (see wpt_film_reduce below)
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommInitAll) CommInitAll = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclReduce) Reduce = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+};
+}  // namespace
+static NcclApi g_nccl;
+static int nccl_load()
+{
+    if (g_nccl.lib) return WPT_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(WPT_E_STATE, std::string("NCCL not available: ") + dlerror());
+    auto sym = [&](const char *n) { return dlsym(h, n); };
+    g_nccl.GetUniqueId = reinterpret_cast<decltype(g_nccl.GetUniqueId)>(sym("ncclGetUniqueId"));
+    g_nccl.CommInitRank = reinterpret_cast<decltype(g_nccl.CommInitRank)>(sym("ncclCommInitRank"));
+    g_nccl.CommInitAll = reinterpret_cast<decltype(g_nccl.CommInitAll)>(sym("ncclCommInitAll"));
+    g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(sym("ncclCommDestroy"));
+    g_nccl.Reduce = reinterpret_cast<decltype(g_nccl.Reduce)>(sym("ncclReduce"));
+    g_nccl.AllGather = reinterpret_cast<decltype(g_nccl.AllGather)>(sym("ncclAllGather"));
+    g_nccl.GroupStart = reinterpret_cast<decltype(g_nccl.GroupStart)>(sym("ncclGroupStart"));
+    g_nccl.GroupEnd = reinterpret_cast<decltype(g_nccl.GroupEnd)>(sym("ncclGroupEnd"));
+    g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(sym("ncclGetErrorString"));
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce || !g_nccl.AllGather ||
+        !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.GetErrorString)
+        return fail(WPT_E_STATE, "NCCL library lacks a required symbol");
+    g_nccl.lib = h;
+    return WPT_OK;
+}
+#define WPT_NCCL(call)                                                                              \
+    do {                                                                                            \
+        ncclResult_t e_ = (call);                                                                   \
+        if (e_ != ncclSuccess) return fail(WPT_E_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(e_)); \
+    } while (0)
+
+// fused tail: 0 = automatic — from bounce 2 on when a pass holds at most 2^25 paths (late bounces of small passes are
+// where a launch's fixed ramp-up/drain cost shows: C3 at 8 spp per GPU +0.9 %), off for larger passes (64 spp: -1 %);
+// measured in profiles/r2_grid_c3.txt
+constexpr int kDefaultTailFrom = 0;
+constexpr uint64_t kAutoTailMaxPaths = 1ull << 25;
 struct wpt_renderer {
     const wpt_scene *scene = nullptr;
     int W = 0, H = 0, spp_per_pass = 1;
@@ -475,8 +561,13 @@ struct wpt_renderer {
     float *depth = nullptr, *seed = nullptr;
     int seeding = 1;
     float seed_margin = 1.0005f;
+    // sharded depth pre-pass (wpt_renderer_set_depth_shard): this rank traces lanes [rank*chunk, (rank+1)*chunk) of the
+    // pixel-centre rays; the hit distances of all ranks are all-gathered (NCCL) into tlane
+    void *shard_comm = nullptr;
+    int shard_rank = 0, shard_n = 1;
+    float *tlane = nullptr;
     // fused tail (wpt_renderer_set_tail): bounces >= tail_from of a pass run in ONE launch of trace_wq<TailIO>
-    int tail_from = kDefaultTailFrom;
+    int tail_from = kDefaultTailFrom, tail_used = -1;
     // overlap mode (wpt_renderer_set_tuning, third knob): a second set of queues on its own stream; passes
     // alternate between the two lanes so that the HBM-bound shade/raygen kernels of one overlap the
     // issue-bound trace kernel of the other.  Each lane then holds half of spp_per_pass.
@@ -505,7 +596,7 @@ extern "C" void wpt_renderer_destroy(wpt_renderer *r)
     if (r->scene && r->scene->device >= 0) cudaSetDevice(r->scene->device);
     for (int k = 0; k < 2; k++) { cudaFree(r->q[k].a); cudaFree(r->q[k].b); cudaFree(r->q[k].c); }
     cudaFree(r->hits); cudaFree(r->counters); cudaFree(r->live_acc); cudaFree(r->film);
-    cudaFree(r->depth); cudaFree(r->seed);
+    cudaFree(r->depth); cudaFree(r->seed); cudaFree(r->tlane);
     for (int k = 0; k < 2; k++) { cudaFree(r->q1[k].a); cudaFree(r->q1[k].b); cudaFree(r->q1[k].c); }
     cudaFree(r->hits1); cudaFree(r->counters1); cudaFree(r->live_acc1);
     for (int k = 0; k < 2; k++) {
@@ -572,11 +663,27 @@ extern "C" int wpt_renderer_set_depth_seeding(wpt_renderer *r, int on)
     return WPT_OK;
 }
 
+extern "C" int wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, int rank, int n_ranks)
+{
+    if (!r) return fail(WPT_E_INVALID, "null renderer");
+    if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_renderer_set_depth_shard: render in flight");
+    if (!nccl_comm || n_ranks <= 1) { r->shard_comm = nullptr; r->shard_rank = 0; r->shard_n = 1; return WPT_OK; }
+    if (rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_renderer_set_depth_shard: bad rank");
+    if (int rc = nccl_load()) return rc;
+    if (!r->tlane) {
+        const uint64_t N = (uint64_t)r->W * r->H, chunk = (N + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+        WPT_CUDA(cudaSetDevice(r->scene->device));
+        WPT_CUDA(cudaMalloc(&r->tlane, sizeof(float) * chunk * (uint64_t)n_ranks));
+    }
+    r->shard_comm = nccl_comm; r->shard_rank = rank; r->shard_n = n_ranks;
+    return WPT_OK;
+}
+
 extern "C" int wpt_renderer_set_tail(wpt_renderer *r, int first_bounce)
 {
     if (!r) return fail(WPT_E_INVALID, "null renderer");
     if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_renderer_set_tail: render in flight");
-    r->tail_from = first_bounce == 0 ? kDefaultTailFrom : first_bounce;
+    r->tail_from = first_bounce;
     return WPT_OK;
 }
 
@@ -674,16 +781,29 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     // where the pre-pass is a small fraction of the frame.
     const bool seeded = r->seeding && cam->lens_radius == 0.0f && cfg->spp_count >= 8 && cfg->tmax >= 1e20f;
     if (seeded) {
+        // every rank of a sharded frame needs the same seeds: with wpt_renderer_set_depth_shard each rank traces 1/n of the
+        // pixel-centre rays and the hit distances are all-gathered, instead of every rank repeating the whole pre-pass
+        const bool shard = r->shard_comm && r->shard_n > 1 && r->tlane;
+        const uint32_t chunk = shard ? (N + (uint32_t)r->shard_n - 1) / (uint32_t)r->shard_n : N;
+        const uint32_t lane0 = shard ? std::min(N, (uint32_t)r->shard_rank * chunk) : 0u;
+        const uint32_t lanes = shard ? std::min(N - lane0, chunk) : N;
         WPT_CUDA(cudaMemsetAsync(r->counters, 0, sizeof(PassCounters), st));
         WPT_CUDA(mark(0));
-        launch_raygen(*cam, r->W, r->H, 0, 1, cfg->seed, r->q[0], &r->counters->qcount[0], st, nullptr, 1);
+        launch_raygen(*cam, r->W, r->H, 0, 1, cfg->seed, r->q[0], &r->counters->qcount[0], st, nullptr, 1, lane0, std::max(lanes, 1u));
         WPT_CUDA(done());
         WPT_CUDA(mark(1));
         launch_trace_queue(s->view, r->q[0], r->hits, &r->counters->qcount[0], &r->counters->cursor[0], nullptr,
-                           cfg->tmin, cfg->tmax, N, s->num_sms, tune, st);
+                           cfg->tmin, cfg->tmax, std::max(lanes, 1u), s->num_sms, tune, st);
         WPT_CUDA(done());
         WPT_CUDA(mark(0));
-        launch_depth_seeds(r->q[0].a, r->hits, r->W, r->H, r->seed_margin, r->depth, r->seed, st);
+        if (shard) {
+            launch_depth_pack(r->hits, lanes, r->tlane + (size_t)r->shard_rank * chunk, st);
+            WPT_NCCL(g_nccl.AllGather(r->tlane + (size_t)r->shard_rank * chunk, r->tlane, chunk, ncclFloat32,
+                                      reinterpret_cast<ncclComm_t>(r->shard_comm), st));
+            launch_depth_seeds_from_lanes(r->tlane, r->W, r->H, r->seed_margin, r->depth, r->seed, st);
+        } else {
+            launch_depth_seeds(r->q[0].a, r->hits, r->W, r->H, r->seed_margin, r->depth, r->seed, st);
+        }
         WPT_CUDA(done());
         r->launches += 4;
     }
@@ -709,7 +829,11 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
                       seeded ? r->seed : nullptr, 0);
         WPT_CUDA(done());
         r->launches++;
-        const int wave_end = (r->tail_from >= 1 && r->tail_from < cfg->depth) ? r->tail_from : cfg->depth;
+        // (the fused tail shades with constant albedos only: scenes with image textures run the wavefront pair)
+        const int tail_from = s->tex.texels ? -1 : r->tail_from != 0 ? r->tail_from
+                            : ((uint64_t)N * (uint64_t)lane_spp <= kAutoTailMaxPaths ? 2 : -1);
+        const int wave_end = (tail_from >= 1 && tail_from < cfg->depth) ? tail_from : cfg->depth;
+        r->tail_used = wave_end < cfg->depth ? wave_end : -1;
         for (int j = 0; j < wave_end; j++) {
             const RayQueue &qin = q[j & 1], &qout = q[(j + 1) & 1];
             const bool sj = seeded && j == 0;
@@ -728,7 +852,7 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
             WPT_CUDA(mark(2));
             launch_shade(qin, hits, &counters->qcount[j], qout, &counters->qcount[j + 1],
                          reinterpret_cast<const float4 *>(s->d_attr), s->d_albedo, j, cfg->depth, spp_first,
-                         cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, ls, sj);
+                         cfg->seed, film_r, film_g, film_b, n_max, s->num_sms, ls, sj, &s->tex);
             WPT_CUDA(done());
             r->launches += 2;
         }
@@ -780,6 +904,7 @@ extern "C" int wpt_render_finish(wpt_renderer *r, wpt_stats *stats, void *stream
         for (int j = 0; j < r->depth_in_flight; j++) { stats->live[j] += live[j]; stats->segments += live[j]; }
         stats->retraced += live[WPT_MAX_DEPTH];
     }
+    stats->tail_from = r->tail_used;
     stats->passes = r->passes;
     stats->kernel_launches = r->launches;
     if (!r->captured) WPT_CUDA(cudaEventElapsedTime(&stats->ms_total, r->ev_begin, r->ev_end));
@@ -905,7 +1030,7 @@ extern "C" int wpt_shade_step(const wpt_scene *s, uint32_t n, const float *o_xyz
     if (!s->committed) return fail(WPT_E_STATE, "wpt_shade_step: scene not committed");
     WPT_CUDA(cudaSetDevice(s->device));
     launch_shade_streams(n, o_xyz, d_xyz, tri_id, t, u, v, s0, s1, reinterpret_cast<const float4 *>(s->d_attr),
-                         s->d_albedo, next_o, next_d, weight, (cudaStream_t)stream);
+                         s->d_albedo, next_o, next_d, weight, (cudaStream_t)stream, &s->tex);
     WPT_CUDA(cudaGetLastError());
     return WPT_OK;
 }
@@ -923,47 +1048,6 @@ extern "C" int wpt_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, ui
 // the copy already in the process — e.g. the one PyTorch loaded — or the system one), so libwpt.so itself has no
 // link-time dependency on it and single-GPU hosts need no NCCL at all.
 // ------------------------------------------------------------------------------------------------
-namespace {
-struct NcclApi {
-    void *lib = nullptr;
-    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
-    decltype(&ncclCommInitRank) CommInitRank = nullptr;
-    decltype(&ncclCommInitAll) CommInitAll = nullptr;
-    decltype(&ncclCommDestroy) CommDestroy = nullptr;
-    decltype(&ncclReduce) Reduce = nullptr;
-    decltype(&ncclGroupStart) GroupStart = nullptr;
-    decltype(&ncclGroupEnd) GroupEnd = nullptr;
-    decltype(&ncclGetErrorString) GetErrorString = nullptr;
-};
-}  // namespace
-static NcclApi g_nccl;
-static int nccl_load()
-{
-    if (g_nccl.lib) return WPT_OK;
-    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
-    if (!h) return fail(WPT_E_STATE, std::string("NCCL not available: ") + dlerror());
-    auto sym = [&](const char *n) { return dlsym(h, n); };
-    g_nccl.GetUniqueId = reinterpret_cast<decltype(g_nccl.GetUniqueId)>(sym("ncclGetUniqueId"));
-    g_nccl.CommInitRank = reinterpret_cast<decltype(g_nccl.CommInitRank)>(sym("ncclCommInitRank"));
-    g_nccl.CommInitAll = reinterpret_cast<decltype(g_nccl.CommInitAll)>(sym("ncclCommInitAll"));
-    g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(sym("ncclCommDestroy"));
-    g_nccl.Reduce = reinterpret_cast<decltype(g_nccl.Reduce)>(sym("ncclReduce"));
-    g_nccl.GroupStart = reinterpret_cast<decltype(g_nccl.GroupStart)>(sym("ncclGroupStart"));
-    g_nccl.GroupEnd = reinterpret_cast<decltype(g_nccl.GroupEnd)>(sym("ncclGroupEnd"));
-    g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(sym("ncclGetErrorString"));
-    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce ||
-        !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.GetErrorString)
-        return fail(WPT_E_STATE, "NCCL library lacks a required symbol");
-    g_nccl.lib = h;
-    return WPT_OK;
-}
-#define WPT_NCCL(call)                                                                              \
-    do {                                                                                            \
-        ncclResult_t e_ = (call);                                                                   \
-        if (e_ != ncclSuccess) return fail(WPT_E_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(e_)); \
-    } while (0)
-
 extern "C" int wpt_nccl_unique_id(void *id128)
 {
     if (!id128) return fail(WPT_E_INVALID, "wpt_nccl_unique_id: null argument");
@@ -1041,6 +1125,24 @@ extern "C" int wpt_scene_set_texcoords(wpt_scene *s, const float *uvs, const int
         if (uv_triplets[k] >= (int32_t)n_uvs) return fail(WPT_E_INVALID, "texcoord index out of range");
     s->uvs.assign(uvs, uvs + 2 * (size_t)n_uvs);
     s->uvidx.assign(uv_triplets, uv_triplets + 3 * (size_t)s->n_tris);
+    return WPT_OK;
+}
+
+// ImageTexture of one material (src/main.cpp:35-80): the reference only ever builds 1x1 textures (ImageTexture::load is
+// empty, :36-38), its eval is nevertheless the bilinear fetch — available here for real images
+extern "C" int wpt_scene_set_texture(wpt_scene *s, uint32_t material, const float *rgb, uint32_t width, uint32_t height)
+{
+    if (!s || !rgb) return fail(WPT_E_INVALID, "wpt_scene_set_texture: null argument");
+    if (s->committed) return fail(WPT_E_STATE, "wpt_scene_set_texture: call before wpt_scene_commit");
+    const size_t n_mat = s->albedo.size() / 3;
+    if (material >= n_mat) return fail(WPT_E_INVALID, "wpt_scene_set_texture: material out of range");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (1u << 26)) return fail(WPT_E_LIMIT, "wpt_scene_set_texture: bad size");
+    for (size_t k = 0; k < 3 * (size_t)width * height; k++)
+        if (!std::isfinite(rgb[k])) return fail(WPT_E_INVALID, "wpt_scene_set_texture: non-finite texel");
+    if (s->tex_rgb.size() < n_mat) { s->tex_rgb.resize(n_mat); s->tex_w.resize(n_mat, 1u); s->tex_h.resize(n_mat, 1u); }
+    s->tex_rgb[material].assign(rgb, rgb + 3 * (size_t)width * height);
+    s->tex_w[material] = width; s->tex_h[material] = height;
+    if (width * height == 1u) for (int k = 0; k < 3; k++) s->albedo[3 * (size_t)material + k] = rgb[k];   // ImageTexture(color)
     return WPT_OK;
 }
 

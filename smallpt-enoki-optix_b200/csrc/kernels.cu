@@ -48,13 +48,15 @@ __device__ __forceinline__ void lane_to_pixel(uint32_t p, int W, int H, int &x, 
 // through the pixel centre and the lens centre (the depth pre-pass; not a sample of the estimator).
 __global__ void __launch_bounds__(256)
 raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass, uint32_t k0, uint32_t k1,
-              RayQueue q, uint32_t *__restrict__ qcount0, const float *__restrict__ seed, int centre)
+              RayQueue q, uint32_t *__restrict__ qcount0, const float *__restrict__ seed, int centre,
+              uint32_t lane_first, uint32_t lane_count)
 {
-    const uint32_t N = (uint32_t)W * (uint32_t)H;
+    // lanes [lane_first, lane_first + lane_count) of every sample: the whole frame, or one rank's share of the depth pre-pass
+    const uint32_t N = lane_count;
     const uint32_t total = N * (uint32_t)spp_in_pass;
     if (blockIdx.x == 0 && threadIdx.x == 0) *qcount0 = total;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t s_local = i / N, p = i - s_local * N;
+        const uint32_t s_local = i / N, p = lane_first + (i - s_local * N);
         int x, y;
         lane_to_pixel(p, W, H, x, y);
         const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;   // src/main.cpp:379-381
@@ -71,13 +73,16 @@ raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass
 }
 
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
-                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed, int centre)
+                   const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed, int centre,
+                   uint32_t lane_first, uint32_t lane_count)
 {
-    const uint64_t total = (uint64_t)W * H * spp_in_pass;
+    if (lane_count == 0) { lane_first = 0; lane_count = (uint32_t)W * (uint32_t)H; }
+    const uint64_t total = (uint64_t)lane_count * spp_in_pass;
     const uint64_t cap = (uint64_t)device_sms() * 16u;
     const uint32_t blocks = (uint32_t)((total + 255) / 256 < cap ? (total + 255) / 256 : cap);
     raygen_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_first, spp_in_pass, (uint32_t)seed,
-                                                       (uint32_t)(seed >> 32), q, qcount0, tmax_seed, centre);
+                                                       (uint32_t)(seed >> 32), q, qcount0, tmax_seed, centre, lane_first,
+                                                       lane_count);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -110,6 +115,40 @@ depth_seed_kernel(const float *__restrict__ depth, int W, int H, float margin, f
         seed[p] = m < 1e19f ? m * margin : 1e20f;
     }
 }
+// sharded depth pre-pass (wpt_renderer_set_depth_shard): every rank traces the pixel-centre rays of its own lane window
+// and writes their hit distances, in lane order, into its chunk of one buffer; after the all-gather every rank scatters
+// the whole buffer to pixels and derives the same seeds
+__global__ void __launch_bounds__(256)
+depth_pack_kernel(const int4 *__restrict__ hits, uint32_t n, float *__restrict__ tlane)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int4 h = hits[i];
+        tlane[i] = h.x >= 0 ? __int_as_float(h.y) : __int_as_float(0x7f800000);
+    }
+}
+__global__ void __launch_bounds__(256)
+depth_scatter_lanes_kernel(const float *__restrict__ tlane, int W, int H, float *__restrict__ depth)
+{
+    const uint32_t n = (uint32_t)W * (uint32_t)H;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        int x, y;
+        lane_to_pixel(p, W, H, x, y);
+        depth[(uint32_t)y * (uint32_t)W + (uint32_t)x] = tlane[p];
+    }
+}
+void launch_depth_pack(const int4 *hits, uint32_t n, float *tlane_chunk, cudaStream_t st)
+{
+    const uint32_t cap = (uint32_t)device_sms() * 16u, blocks = (n + 255) / 256 < cap ? (n + 255) / 256 : cap;
+    if (n) depth_pack_kernel<<<blocks, 256, 0, st>>>(hits, n, tlane_chunk);
+}
+void launch_depth_seeds_from_lanes(const float *tlane, int W, int H, float margin, float *depth, float *seed, cudaStream_t st)
+{
+    const uint32_t n = (uint32_t)W * (uint32_t)H, cap = (uint32_t)device_sms() * 16u;
+    const uint32_t blocks = (n + 255) / 256 < cap ? (n + 255) / 256 : cap;
+    depth_scatter_lanes_kernel<<<blocks, 256, 0, st>>>(tlane, W, H, depth);
+    depth_seed_kernel<<<blocks, 256, 0, st>>>(depth, W, H, margin, seed);
+}
+
 void launch_depth_seeds(const float4 *qa, const int4 *hits, int W, int H, float margin, float *depth, float *seed,
                         cudaStream_t st)
 {
@@ -150,11 +189,15 @@ void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, u
 // ------------------------------------------------------------------------------------------------
 constexpr int kShadeBlock = 256;
 
+// TEX: some material of the scene carries an image texture (wpt_scene_set_texture): the bsdf weight of such a material
+// is ImageTexture::eval at the interpolated texcoord (src/main.cpp:62-76,116) instead of the constant albedo
+template <bool TEX>
 __global__ void __launch_bounds__(kShadeBlock)
 shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *__restrict__ n_ptr,
              const RayQueue out, uint32_t *__restrict__ n_out, const float4 *__restrict__ tri_attr,
              const float *__restrict__ albedo, int bounce, int depth, int spp_first, uint32_t k0, uint32_t k1,
-             float *__restrict__ film_r, float *__restrict__ film_g, float *__restrict__ film_b, int seeded0)
+             float *__restrict__ film_r, float *__restrict__ film_g, float *__restrict__ film_b, int seeded0,
+             const TexArgs tex)
 {
     __shared__ uint32_t warp_cnt[kShadeBlock / 32];
     __shared__ uint32_t block_base;
@@ -191,8 +234,17 @@ shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *_
                 shade_step(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), __int_as_float(h.y), __int_as_float(h.z),
                            __int_as_float(h.w), v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), v3(q1.z, q1.w, q2.x),
                            u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), no, nd);
-                const float wr = __ldg(albedo + 3 * mat), wg = __ldg(albedo + 3 * mat + 1),
-                            wb = __ldg(albedo + 3 * mat + 2);
+                float wr = __ldg(albedo + 3 * mat), wg = __ldg(albedo + 3 * mat + 1), wb = __ldg(albedo + 3 * mat + 2);
+                if (TEX) {
+                    const MatTex mt = tex.mattex[mat];
+                    if (mt.w * mt.h > 1u) {
+                        const float2 *uv = tex.triuv + (size_t)h.x * 3;
+                        float tu, tv, rgb[3];
+                        interp_uv(__ldg(uv), __ldg(uv + 1), __ldg(uv + 2), __int_as_float(h.z), __int_as_float(h.w), tu, tv);
+                        texture_eval(tex.texels, mt, tu, tv, rgb);
+                        wr = rgb[0]; wg = rgb[1]; wb = rgb[2];
+                    }
+                }
                 na = make_float4(no.x, no.y, no.z, a.w);
                 nb = make_float4(nd.x, nd.y, nd.z, b.w * wr);     // contrib *= bsdf weight (src/main.cpp:422)
                 nc = make_float2(c.x * wg, c.y * wb);
@@ -224,15 +276,20 @@ shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *_
 void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
                   uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
                   int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
-                  int num_sms, cudaStream_t st, int seeded0)
+                  int num_sms, cudaStream_t st, int seeded0, const TexArgs *tex)
 {
     uint32_t blocks = (n_max + kShadeBlock - 1) / kShadeBlock;
     const uint32_t cap = (uint32_t)num_sms * 8u;
     if (blocks > cap) blocks = cap;
     if (blocks == 0) blocks = 1;
-    shade_kernel<<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
-                                                 spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
-                                                 film_g, film_b, seeded0);
+    if (tex && tex->texels)
+        shade_kernel<true><<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
+                                                           spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
+                                                           film_g, film_b, seeded0, *tex);
+    else
+        shade_kernel<false><<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
+                                                            spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
+                                                            film_g, film_b, seeded0, TexArgs{nullptr, nullptr, nullptr});
 }
 
 // per-function entry point: one shading step on SoA streams (parity tests)
@@ -243,7 +300,7 @@ struct ShadeStreams {
     float *no[3], *nd[3], *w[3];
 };
 __global__ void shade_streams_kernel(uint32_t n, ShadeStreams p, const float4 *__restrict__ tri_attr,
-                                     const float *__restrict__ albedo)
+                                     const float *__restrict__ albedo, const TexArgs tex)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -257,17 +314,27 @@ __global__ void shade_streams_kernel(uint32_t n, ShadeStreams p, const float4 *_
                v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), v3(q1.z, q1.w, q2.x), p.s0[i], p.s1[i], no, nd);
     p.no[0][i] = no.x; p.no[1][i] = no.y; p.no[2][i] = no.z;
     p.nd[0][i] = nd.x; p.nd[1][i] = nd.y; p.nd[2][i] = nd.z;
-    p.w[0][i] = albedo[3 * mat]; p.w[1][i] = albedo[3 * mat + 1]; p.w[2][i] = albedo[3 * mat + 2];
+    float w[3] = {albedo[3 * mat], albedo[3 * mat + 1], albedo[3 * mat + 2]};
+    if (tex.texels) {
+        const MatTex mt = tex.mattex[mat];
+        if (mt.w * mt.h > 1u) {
+            const float2 *uv = tex.triuv + (size_t)tri * 3;
+            float tu, tv;
+            interp_uv(uv[0], uv[1], uv[2], p.u[i], p.v[i], tu, tv);
+            texture_eval(tex.texels, mt, tu, tv, w);
+        }
+    }
+    p.w[0][i] = w[0]; p.w[1][i] = w[1]; p.w[2][i] = w[2];
 }
 void launch_shade_streams(uint32_t n, const float *const o[3], const float *const d[3], const int32_t *tri_id,
                           const float *t, const float *u, const float *v, const float *s0, const float *s1,
                           const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
-                          float *const w[3], cudaStream_t st)
+                          float *const w[3], cudaStream_t st, const TexArgs *tex)
 {
     ShadeStreams p;
     for (int k = 0; k < 3; k++) { p.o[k] = o[k]; p.d[k] = d[k]; p.no[k] = no[k]; p.nd[k] = nd[k]; p.w[k] = w[k]; }
     p.tri_id = tri_id; p.t = t; p.u = u; p.v = v; p.s0 = s0; p.s1 = s1;
-    if (n) shade_streams_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, p, tri_attr, albedo);
+    if (n) shade_streams_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, p, tri_attr, albedo, tex ? *tex : TexArgs{nullptr, nullptr, nullptr});
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -43,6 +43,14 @@ struct TailArgs {
     uint64_t seed;
 };
 
+// image textures (wpt_scene_set_texture): per-material window into one texel pool, per-triangle texcoords
+struct MatTex;
+struct TexArgs {
+    const float4 *texels;     // null: no material of the scene has an image texture
+    const MatTex *mattex;     // per material
+    const float2 *triuv;      // 3 per ORIGINAL triangle
+};
+
 // wpt_hit_attributes (src/accel/optix_backend.h:463-486): device streams; any output group may be null
 struct HitAttrArgs {
     const float *ox, *oy, *oz, *dx, *dy, *dz;
@@ -80,7 +88,9 @@ void launch_trace_tail(const BvhView &bvh, const RayQueue &q, const uint32_t *n_
 void launch_hit_attributes(uint32_t n, const HitAttrArgs &a, cudaStream_t st);
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
                    const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed = nullptr,
-                   int centre = 0);
+                   int centre = 0, uint32_t lane_first = 0, uint32_t lane_count = 0);
+void launch_depth_pack(const int4 *hits, uint32_t n, float *tlane_chunk, cudaStream_t st);
+void launch_depth_seeds_from_lanes(const float *tlane, int W, int H, float margin, float *depth, float *seed, cudaStream_t st);
 void launch_depth_seeds(const float4 *qa, const int4 *hits, int W, int H, float margin, float *depth, float *seed,
                         cudaStream_t st);
 void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, uint64_t seed, float *ox,
@@ -88,11 +98,11 @@ void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, u
 void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, const RayQueue &out,
                   uint32_t *n_out, const float4 *tri_attr, const float *albedo, int bounce, int depth,
                   int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
-                  int num_sms, cudaStream_t st, int seeded0 = 0);
+                  int num_sms, cudaStream_t st, int seeded0 = 0, const TexArgs *tex = nullptr);
 void launch_shade_streams(uint32_t n, const float *const o[3], const float *const d[3], const int32_t *tri_id,
                           const float *t, const float *u, const float *v, const float *s0, const float *s1,
                           const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
-                          float *const w[3], cudaStream_t st);
+                          float *const w[3], cudaStream_t st, const TexArgs *tex = nullptr);
 void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st);
 void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
                   const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,

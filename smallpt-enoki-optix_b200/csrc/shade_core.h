@@ -134,6 +134,47 @@ WPT_HD void camera_ray(const wpt_camera &c, int px, int py, int W, int H, const 
              fmaf(c.z[2], d.z, fmaf(c.y[2], d.y, c.x[2] * d.x)));
 }
 
+// ---------------------------------------------------------------- ImageTexture::eval (src/main.cpp:62-76)
+// Bilinear fetch with clamped coordinates (texel_fetch_wrap, :56-60).  The reference's texel_fetch computes
+// pixel_index = y * m_image_size.y() + x (:52) — wrong for non-square images (it should be the ROW LENGTH, size.x);
+// fixed here and in the oracle, noted in DESIGN.md.  Operation order as written there: scaled = uv * size - 0.5,
+// pos = floor, d1 = scaled - pos, d2 = 1 - d1, sum of four texel * dx * dy products left to right, no FMA.
+struct MatTex { uint32_t offset, w, h, pad; };     // texel pool window of one material; w * h == 1: constant albedo
+#if defined(__CUDA_ARCH__)
+#define WPT_MUL(a, b) __fmul_rn(a, b)
+#define WPT_ADD(a, b) __fadd_rn(a, b)
+#define WPT_SUB(a, b) __fsub_rn(a, b)
+#else
+#define WPT_MUL(a, b) ((a) * (b))
+#define WPT_ADD(a, b) ((a) + (b))
+#define WPT_SUB(a, b) ((a) - (b))
+#endif
+WPT_HD void texture_eval(const float4 *texels, const MatTex mt, float tu, float tv, float rgb[3])
+{
+    const float su = WPT_SUB(WPT_MUL(tu, (float)mt.w), 0.5f), sv = WPT_SUB(WPT_MUL(tv, (float)mt.h), 0.5f);
+    const float fx = floorf(su), fy = floorf(sv);
+    const int x = (int)fx, y = (int)fy;
+    const float dx1 = WPT_SUB(su, fx), dy1 = WPT_SUB(sv, fy);
+    const float dx2 = WPT_SUB(1.0f, dx1), dy2 = WPT_SUB(1.0f, dy1);
+    const int W = (int)mt.w, H = (int)mt.h;
+    const int x0 = x < 0 ? 0 : (x > W - 1 ? W - 1 : x), x1 = x + 1 < 0 ? 0 : (x + 1 > W - 1 ? W - 1 : x + 1);
+    const int y0 = y < 0 ? 0 : (y > H - 1 ? H - 1 : y), y1 = y + 1 < 0 ? 0 : (y + 1 > H - 1 ? H - 1 : y + 1);
+    const float4 *t = texels + mt.offset;
+    const float4 t00 = t[y0 * W + x0], t01 = t[y1 * W + x0], t10 = t[y0 * W + x1], t11 = t[y1 * W + x1];
+#define WPT_BILERP(C)                                                                                            \
+    WPT_ADD(WPT_ADD(WPT_ADD(WPT_MUL(WPT_MUL(t00.C, dx2), dy2), WPT_MUL(WPT_MUL(t01.C, dx2), dy1)),                   \
+                    WPT_MUL(WPT_MUL(t10.C, dx1), dy2)), WPT_MUL(WPT_MUL(t11.C, dx1), dy1))
+    rgb[0] = WPT_BILERP(x); rgb[1] = WPT_BILERP(y); rgb[2] = WPT_BILERP(z);
+#undef WPT_BILERP
+}
+// interpolated texture coordinate of a hit (src/accel/optix_backend.h:479-480, src/add_math.h:3-7)
+WPT_HD void interp_uv(const float2 a, const float2 b, const float2 c, float u, float v, float &tu, float &tv)
+{
+    const float w = WPT_SUB(WPT_SUB(1.0f, u), v);
+    tu = WPT_ADD(WPT_ADD(WPT_MUL(w, a.x), WPT_MUL(u, b.x)), WPT_MUL(v, c.x));
+    tv = WPT_ADD(WPT_ADD(WPT_MUL(w, a.y), WPT_MUL(u, b.y)), WPT_MUL(v, c.y));
+}
+
 // ---------------------------------------------------------------- one shading step
 // src/accel/optix_backend.h:469 (p = o + t d), :412-420 + src/add_math.h:3-7 (un-normalised
 // interpolated shading normal), src/main.cpp:414-424.  No FMA where the reference has none.

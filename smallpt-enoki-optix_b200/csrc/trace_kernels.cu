@@ -633,8 +633,8 @@ static void launch_wq(const BvhView &bvh, const IO &io, const uint32_t *n_ptr, u
 }
 
 // tune.variant: 0 default | 1 one thread per ray | 2 per-lane triangle loop | 12 default with a two-row shared stack
-// (exercises the local-memory overflow) | 20 per-entry flush (the round-1 kernel) | 21..23 balanced flush with refill
-// thresholds 20 / 24 / 28.  Variants 1 and 2 exist for plain ray sources only; every other source runs the default.
+// (exercises the local-memory overflow) | 20 per-entry flush (the round-1 kernel) | 21..26 balanced flush with refill
+// thresholds 20 / 24 / 28 / 16 / 18 / 22.  Variants 1 and 2 exist for plain ray sources only; every other source runs the default.
 template <class IO>
 static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n_ptr, uint32_t n_static,
                              uint32_t *cursor, unsigned long long *live_acc, int num_sms,
@@ -657,6 +657,9 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
     case 21: launch_wq<IO, 20, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
     case 22: launch_wq<IO, 24, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
     case 23: launch_wq<IO, 28, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
+    case 24: launch_wq<IO, 16, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
+    case 25: launch_wq<IO, 18, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
+    case 26: launch_wq<IO, 22, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
     default: launch_wq<IO, kDefaultThresh, 8, kDefaultFlush>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); break;
     }
 }

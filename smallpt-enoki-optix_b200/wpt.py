@@ -68,7 +68,8 @@ class RenderConfig(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("segments", C.c_uint64), ("live", C.c_uint64 * WPT_MAX_DEPTH), ("passes", C.c_uint32),
                 ("kernel_launches", C.c_uint32), ("ms_total", C.c_float), ("ms_raygen", C.c_float),
-                ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("retraced", C.c_uint64)]
+                ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("retraced", C.c_uint64), ("tail_from", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 _lib = None
@@ -255,6 +256,13 @@ class Scene:
             _check(lib().wpt_scene_set_texcoords(self._h, C.c_void_p(uv.ctypes.data), C.c_void_p(uvi.ctypes.data),
                                                  C.c_uint32(uv.size // 2)))
 
+    def set_texture(self, material, image):
+        """ImageTexture of one material (src/main.cpp:35-80): image float32 (h, w, 3); before commit()"""
+        img = _np(image, np.float32)
+        assert img.ndim == 3 and img.shape[2] == 3
+        _check(lib().wpt_scene_set_texture(self._h, C.c_uint32(material), C.c_void_p(img.ctypes.data),
+                                           C.c_uint32(img.shape[1]), C.c_uint32(img.shape[0])))
+
     def commit(self, device=0):
         if not self._h:
             raise WptError(3, "Scene.commit: no mesh")
@@ -401,6 +409,11 @@ class Renderer:
     def set_depth_seeding(self, on=True):
         """True / False, or an int > 1 = seed margin in 1/10000 (tests)"""
         _check(lib().wpt_renderer_set_depth_seeding(self._h, C.c_int(int(on))))
+
+    def set_depth_shard(self, comm, rank, n_ranks):
+        """wpt_renderer_set_depth_shard: rank `rank` of `n_ranks` traces its share of the depth pre-pass, the hit distances
+        are all-gathered on `comm` (a wpt_nccl communicator handle) inside render()"""
+        _check(lib().wpt_renderer_set_depth_shard(self._h, comm, C.c_int(rank), C.c_int(n_ranks)))
 
     def set_tail(self, first_bounce=0):
         """bounces >= first_bounce run in one fused trace+shade launch per pass; 0 = default, negative = off"""

@@ -1,0 +1,73 @@
+"""-m gpu, two GPUs (skipped on a one-GPU box; run under `gpurun --gpus 2`): the N>1 data plane of the product —
+one process per GPU, samples sharded by the global index, the depth pre-pass sharded over the ranks with one
+ncclAllGather inside wpt_render, ONE wpt_film_reduce (ncclReduce on libwpt's own communicator) — equals the one-GPU frame.
+torch.distributed (gloo) only ships the 128-byte NCCL id."""
+import os
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, q):
+    here = os.path.dirname(os.path.abspath(__file__))
+    root = os.path.dirname(here)
+    for p in (os.path.join(root, "oracle"), os.path.join(root, "smallpt-enoki-optix_b200"), here):
+        sys.path.insert(0, p)
+    import torch
+    import torch.distributed as dist
+    import scenes
+    import wpt
+    import wpt_dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    red = wpt_dist.FilmReducer(rank)
+    sd = scenes.knob(120, 50)
+    scene = wpt.scene_from(sd, device=rank)
+    cam = wpt.camera_from(sd)
+    W, H, spp, depth = 160, 128, 24, 6
+    out = []
+    for shard in (0, 1):
+        r = wpt.Renderer(scene, W, H, 8)
+        if shard:
+            r.set_depth_shard(red.comm, rank, world)
+        b, c = wpt_dist.spp_range_strong(rank, world, spp)
+        film = torch.zeros(3, W * H, device="cuda")
+        r.render(cam, film, b, c, depth, seed=9)
+        red.reduce(film, 0)
+        st = r.finish()
+        segs = torch.tensor([st["segments"], st["retraced"]], dtype=torch.int64)
+        dist.reduce(segs, dst=0)
+        out.append((film, segs))
+        r.close()
+    if rank == 0:
+        r = wpt.Renderer(scene, W, H, 8)
+        whole = torch.zeros(3, W * H, device="cuda")
+        r.render(cam, whole, 0, spp, depth, seed=9)
+        st = r.finish()
+        ok = [bool(torch.allclose(f, whole, rtol=0, atol=2e-5)) and int(s[0]) == st["segments"] for f, s in out]
+        # sharded and unsharded pre-pass give the same seeds: the same rays are traced a second time
+        q.put((ok, int(out[0][1][1]) == int(out[1][1][1]), float(whole.sum()) > 0))
+    red.close()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharded_frame_equals_one_gpu():
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run under gpurun --gpus 2)")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res == ([True, True], True, True)

@@ -179,3 +179,29 @@ def test_spp_ranges_compose_pcg_and_philox():
         a, s1 = om.render("bvh", cam, 24, 24, 0, 2, 4, rng_mode=mode, seed=9)
         b, s2 = om.render("bvh", cam, 24, 24, 2, 4, 4, rng_mode=mode, seed=9)
         assert np.array_equal(whole, a + b) and s == s1 + s2
+
+
+def test_texture_eval_restatement():
+    """ImageTexture::eval (src/main.cpp:62-76) as restated: a 1x1 texture is the constant the reference builds for every
+    material (weights sum to 1 within 2 ulp); texel centres reproduce the texel; the midpoint of four texels is their
+    mean; coordinates clamp (texel_fetch_wrap :56-60); a NON-square image is indexed by its row length (the :52 bug)."""
+    import ctypes as C
+    L = O.lib()
+
+    def ev(img, u, v):
+        img = np.ascontiguousarray(img, np.float32)
+        t = O.OrcTexture(img.ctypes.data, img.shape[1], img.shape[0])
+        out = (C.c_float * 3)()
+        L.orc_texture_eval(C.byref(t), C.c_float(u), C.c_float(v), out)
+        return np.array(out, np.float32)
+
+    rng = np.random.default_rng(0)
+    one = np.array([[[0.25, 0.5, 0.75]]], np.float32)
+    for u, v in rng.random((50, 2)):
+        assert np.abs(ev(one, u, v) - one[0, 0]).max() <= 2 * np.finfo(np.float32).eps
+    img = rng.random((5, 8, 3)).astype(np.float32)          # h = 5, w = 8: non-square
+    for y in range(5):
+        for x in range(8):
+            assert np.allclose(ev(img, (x + 0.5) / 8, (y + 0.5) / 5), img[y, x], atol=1e-6)
+    assert np.allclose(ev(img, 3.0 / 8, 2.0 / 5), img[1:3, 2:4].reshape(-1, 3).mean(0), atol=1e-6)
+    assert np.allclose(ev(img, -3.0, 9.0), img[4, 0], atol=1e-6) and np.allclose(ev(img, 2.0, -1.0), img[0, 7], atol=1e-6)
