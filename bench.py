@@ -355,6 +355,7 @@ def run_ours(args):
     if rank == 0:
         # per-kernel events need serial kernels: single lane, the kernel's own occupancy (8 CTAs/SM)
         r.set_tuning(args.variant, args.ctas_per_sm, 0)
+        r.set_depth_shard(None, 0, 1)          # this frame runs on rank 0 alone: no collective inside wpt_render
         r.set_profile(True)
         film.zero_()
         r.render(cam, film, spp_begin, spp, depth, seed=SEED)

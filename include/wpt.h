@@ -216,7 +216,7 @@ int  wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, int rank, in
  * fused in (a path whose segment ends is shaded by its own lane and continues in place) instead of one trace + one
  * shade launch per bounce — late bounces hold few paths and a persistent launch has a fixed ramp-up/drain cost.
  * Same Philox counters, same paths, same film up to fp32 atomic order.  first_bounce >= 1; negative = off (a wavefront
- * launch pair for every bounce); 0 = automatic (default): from bounce 2 on when a pass holds at most 2^25 paths, off
+ * launch pair for every bounce); 0 = automatic (default): from bounce 2 on when a pass holds at most 2^24 paths, off
  * for larger passes, where it does not pay (profiles/r2_grid_c3.txt). */
 int  wpt_renderer_set_tail(wpt_renderer *r, int first_bounce);
 /* Tuning knobs (0 = default): which trace kernel; CTAs per SM of a trace launch; overlap_lanes != 0 renders

@@ -542,11 +542,11 @@ static int nccl_load()
         if (e_ != ncclSuccess) return fail(WPT_E_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(e_)); \
     } while (0)
 
-// fused tail: 0 = automatic — from bounce 2 on when a pass holds at most 2^25 paths (late bounces of small passes are
+// fused tail: 0 = automatic — from bounce 2 on when a pass holds at most 2^24 paths (late bounces of small passes are
 // where a launch's fixed ramp-up/drain cost shows: C3 at 8 spp per GPU +0.9 %), off for larger passes (64 spp: -1 %);
 // measured in profiles/r2_grid_c3.txt
 constexpr int kDefaultTailFrom = 0;
-constexpr uint64_t kAutoTailMaxPaths = 1ull << 25;
+constexpr uint64_t kAutoTailMaxPaths = 1ull << 24;
 struct wpt_renderer {
     const wpt_scene *scene = nullptr;
     int W = 0, H = 0, spp_per_pass = 1;

@@ -122,9 +122,10 @@ int main(int, char **v) {
     Interaction it(n);
     sc.intersect(ray, nullptr, 0, it);
     auto id = it.m_hit.m_tri_id.to_host(); auto pz = it.m_hit.m_position[2].to_host(); auto gz = it.m_hit.m_geometry_normal[2].to_host();
+    auto gx = it.m_hit.m_geometry_normal[0].to_host(); auto gy = it.m_hit.m_geometry_normal[1].to_host();
     auto mat = it.m_scatter.to_host(); auto t = it.m_hit.m_t.to_host();
     int hits = 0; double err = 0;
-    for (uint32_t i = 0; i < n; i++) if (id[i] >= 0) { hits++; err += std::fabs(pz[i] - (4.f - t[i])) + (mat[i] < 0) + (std::fabs(std::fabs(gz[i]) - 1.f) > 1e-5f && std::fabs(gz[i]) > 1e-5f); }
+    for (uint32_t i = 0; i < n; i++) if (id[i] >= 0) { hits++; err += std::fabs(pz[i] - (4.f - t[i])) + (mat[i] < 0) + (std::fabs(std::sqrt(gx[i] * gx[i] + gy[i] * gy[i] + gz[i] * gz[i]) - 1.f) > 1e-5f); }
     std::printf("%d %g\\n", hits, err);
     return 0; }
 ''')
