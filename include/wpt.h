@@ -32,6 +32,11 @@ enum {
 
 const char *wpt_last_error(void);
 int wpt_version(void);
+/* Self-checking build (make libwpt_checked.so, -DWPT_CHECKS): the traversal kernels count violations of their own
+ * invariants — warp-queue / item / stack slots in range, block indices inside the tree, ray indices inside the queue,
+ * queue empty after a drain — per kind in out[8]; reset != 0 zeroes them.  WPT_E_STATE in the product build, whose
+ * kernels carry no checks. */
+int wpt_debug_check_failures(uint32_t out[8], int reset);
 
 /* ------------------------------------------------------------------ scene
  * Replaces Scene::add_triangle_mesh's device upload (src/main.cpp:288-310) and

@@ -43,6 +43,17 @@ struct NvtxRange {
 extern "C" const char *wpt_last_error(void) { return g_err.c_str(); }
 extern "C" int wpt_version(void) { return WPT_VERSION; }
 
+// libwpt_checked.so (built with -DWPT_CHECKS): the traversal kernels count violations of their own invariants (queue /
+// item / stack slots, block indices, ray indices); out[8] receives the counters per kind.  WPT_E_STATE in the product build.
+extern "C" int wpt_debug_check_failures(uint32_t out[8], int reset)
+{
+    if (!out) return fail(WPT_E_INVALID, "wpt_debug_check_failures: null argument");
+    const int rc = read_check_failures(out, reset);
+    if (rc < 0) return fail(WPT_E_STATE, "wpt_debug_check_failures: this libwpt was built without WPT_CHECKS");
+    if (rc > 0) return fail(WPT_E_CUDA, "wpt_debug_check_failures: cannot read the counters");
+    return WPT_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kCursorRing = 4096;
 struct wpt_scene {

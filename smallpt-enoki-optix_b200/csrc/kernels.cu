@@ -10,8 +10,10 @@
 #include "kernels.cuh"
 #include "shade_core.h"
 #include "trace_core.h"
+#include <cstdlib>
 
 namespace wpt {
+constexpr int kDefaultShadeBlocks = 6;   // measured (profiles/r2_grid_c3.txt): 6 blocks at 40 registers 7.2 ms of shade per C3 frame, 8 at 32 registers 7.5 ms; a grid of 8 per SM on 6 resident (round 1) 8.05 ms
 
 // SM count of the current device (grid sizing of the grid-stride stream kernels), cached per device
 static int device_sms()
@@ -191,8 +193,8 @@ constexpr int kShadeBlock = 256;
 
 // TEX: some material of the scene carries an image texture (wpt_scene_set_texture): the bsdf weight of such a material
 // is ImageTexture::eval at the interpolated texcoord (src/main.cpp:62-76,116) instead of the constant albedo
-template <bool TEX>
-__global__ void __launch_bounds__(kShadeBlock)
+template <bool TEX, int MINB>
+__global__ void __launch_bounds__(kShadeBlock, MINB)
 shade_kernel(const RayQueue in, const int4 *__restrict__ hits, const uint32_t *__restrict__ n_ptr,
              const RayQueue out, uint32_t *__restrict__ n_out, const float4 *__restrict__ tri_attr,
              const float *__restrict__ albedo, int bounce, int depth, int spp_first, uint32_t k0, uint32_t k1,
@@ -278,18 +280,19 @@ void launch_shade(const RayQueue &in, const int4 *hits, const uint32_t *n_ptr, c
                   int spp_first, uint64_t seed, float *film_r, float *film_g, float *film_b, uint32_t n_max,
                   int num_sms, cudaStream_t st, int seeded0, const TexArgs *tex)
 {
+    // resident blocks per SM: 6 at the compiler's 40 registers, 8 when held to 32 (16 bytes of spill); WPT_SHADE_BLOCKS
+    // selects (experiments), default = measured winner (profiles/r2_stream_kernels_ncu.txt)
+    static const int minb = [] { const char *e = getenv("WPT_SHADE_BLOCKS"); return e ? atoi(e) : kDefaultShadeBlocks; }();
     uint32_t blocks = (n_max + kShadeBlock - 1) / kShadeBlock;
-    const uint32_t cap = (uint32_t)num_sms * 8u;
+    const uint32_t cap = (uint32_t)num_sms * (uint32_t)(minb >= 8 ? 8 : 6);
     if (blocks > cap) blocks = cap;
     if (blocks == 0) blocks = 1;
-    if (tex && tex->texels)
-        shade_kernel<true><<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
-                                                           spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
-                                                           film_g, film_b, seeded0, *tex);
-    else
-        shade_kernel<false><<<blocks, kShadeBlock, 0, st>>>(in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth,
-                                                            spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r,
-                                                            film_g, film_b, seeded0, TexArgs{nullptr, nullptr, nullptr});
+    const TexArgs none{nullptr, nullptr, nullptr};
+#define WPT_SHADE_ARGS in, hits, n_ptr, out, n_out, tri_attr, albedo, bounce, depth, spp_first, (uint32_t)seed, (uint32_t)(seed >> 32), film_r, film_g, film_b, seeded0
+    if (tex && tex->texels) shade_kernel<true, 4><<<blocks, kShadeBlock, 0, st>>>(WPT_SHADE_ARGS, *tex);
+    else if (minb >= 8) shade_kernel<false, 8><<<blocks, kShadeBlock, 0, st>>>(WPT_SHADE_ARGS, none);
+    else shade_kernel<false, 6><<<blocks, kShadeBlock, 0, st>>>(WPT_SHADE_ARGS, none);
+#undef WPT_SHADE_ARGS
 }
 
 // per-function entry point: one shading step on SoA streams (parity tests)

@@ -85,6 +85,8 @@ void launch_trace_streams(const BvhView &bvh, const StreamIO &io, uint32_t n, ui
 void launch_trace_tail(const BvhView &bvh, const RayQueue &q, const uint32_t *n_ptr, uint32_t *cursor,
                        unsigned long long *live_acc, const TailArgs &a, uint32_t n_max, int num_sms,
                        const TraceTuning &tune, cudaStream_t st);
+// WPT_CHECKS build only: per-kind counters of violated invariants (-1 in the product build)
+int read_check_failures(unsigned int out[8], int reset);
 void launch_hit_attributes(uint32_t n, const HitAttrArgs &a, cudaStream_t st);
 void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_in_pass, uint64_t seed,
                    const RayQueue &q, uint32_t *qcount0, cudaStream_t st, const float *tmax_seed = nullptr,

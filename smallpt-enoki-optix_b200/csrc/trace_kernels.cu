@@ -15,6 +15,26 @@
 
 namespace wpt {
 
+// WPT_CHECKS build (libwpt_checked.so, tests/test_gpu_checked.py): compute-sanitizer is closed on this pool, so the
+// invariants its memcheck / racecheck would watch in the warp-queue code are asserted by the kernel itself and counted
+// per kind; wpt_debug_check_failures() reads the counters.  The product build compiles the checks away.
+#ifdef WPT_CHECKS
+__device__ unsigned int g_check_fail[8];
+#define WPT_CHECK(cond, code) do { if (!(cond)) atomicAdd(&g_check_fail[code], 1u); } while (0)
+int read_check_failures(unsigned int out[8], int reset)
+{
+    if (cudaMemcpyFromSymbol(out, g_check_fail, sizeof(unsigned int) * 8) != cudaSuccess) return 1;
+    if (reset) { unsigned int z[8] = {0}; if (cudaMemcpyToSymbol(g_check_fail, z, sizeof z) != cudaSuccess) return 1; }
+    return 0;
+}
+#else
+#define WPT_CHECK(cond, code) ((void)0)
+int read_check_failures(unsigned int *, int) { return -1; }
+#endif
+// check kinds: 0 queue slot out of range | 1 item slot out of range | 2 block index beyond the tree | 3 traversal
+// stack out of range | 4 fetched ray index beyond the queue | 5 queue not empty after a drain | 6 item count differs
+// from the scanned total | 7 owner lane of a queued entry out of range
+
 // ------------------------------------------------------------------------------------------------
 // ray sources / hit sinks
 // ------------------------------------------------------------------------------------------------
@@ -367,9 +387,12 @@ __device__ __forceinline__ void flush_queue_balanced(const BvhView &bvh, WarpSha
         }
         const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
         uint32_t pos = incl - c;
+        WPT_CHECK(__reduce_add_sync(0xffffffffu, c) == total, 6);
         while (T && pos < (uint32_t)kItemCap) {
             const uint32_t tb = bfind_u32(T);
             T ^= 1u << tb;
+            WPT_CHECK(pos < (uint32_t)kItemCap, 1);
+            WPT_CHECK((ex & 0x07ffffffu) + tb < bvh.n_blocks, 2);
             ws.items[pos++] = ex + tb;      // owner << 27 | (first block + tb): blocks < 2^27 (wpt_scene_commit)
         }
         __syncwarp();
@@ -379,8 +402,11 @@ __device__ __forceinline__ void flush_queue_balanced(const BvhView &bvh, WarpSha
             uint32_t owner = 0, prim = 0;
             float t = 0.0f, u = 0.0f, v = 0.0f;
             if (base + lane < m) {
+                WPT_CHECK(base + lane < (uint32_t)kItemCap, 1);
                 const uint32_t it = ws.items[base + lane];
                 owner = it >> 27;
+                WPT_CHECK(owner < 32u, 7);
+                WPT_CHECK((it & 0x07ffffffu) < bvh.n_blocks, 2);
                 const float4 ra = ws.ray_a[owner], rb = ws.ray_b[owner];
                 RayCtx r;
                 r.ox = ra.x; r.oy = ra.y; r.oz = ra.z; r.dx = ra.w; r.dy = rb.x; r.dz = rb.y; r.tmin = rb.z;
@@ -481,6 +507,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             // drain the queue so that parked rays are final, finish them, then refill
             if (qn) {
                 do flush_queue<FLUSH>(bvh, ws, lane, qn, qn < 32u ? qn : 32u); while (qn);
+                WPT_CHECK(qn == 0u, 5);
                 tmax_r = ws_tmax(ws, lane);
             }
             if (state == 2) {
@@ -509,6 +536,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
                     if (state == 0) {
                         const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
                         float ox, oy, oz, dx, dy, dz, t0, t1;
+                        WPT_CHECK(i < n || exhausted, 4);
                         if (i < n && io_load(io, i, ox, oy, oz, dx, dy, dz, t0, t1, ps, lane)) {
                             arm(ox, oy, oz, dx, dy, dz, t0, t1);
                             ray_i = i;
@@ -529,11 +557,13 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const uint32_t bit = bfind_u32(G.y);
             G.y ^= 1u << bit;
             if (G.y >> 24) {
+                WPT_CHECK(DEEP ? (s_top < s_limit || (s_top - s_limit) / kRow < (uint32_t)(kStackSize - SST)) : s_top < s_limit, 3);
                 if (!DEEP || s_top < s_limit) sts64(s_top, G); else lstack[(s_top - s_limit) / kRow] = G;
                 s_top += kRow;
             }
             const uint32_t slot = (bit ^ r.oct_inv) & 7u;       // = (bit - 24) ^ oct_inv
             const uint32_t rel = (uint32_t)__popc(G.y & ((1u << slot) - 1u) & 0xffu);
+            WPT_CHECK(G.x + rel < bvh.n_blocks, 2);
             const uint4 *np = bvh.blocks + (size_t)(G.x + rel) * 4;
             uint4 q0, q1, q2, q3;
             ld_half_m<0>(np, q0, q1); ld_half_m<0>(np + 2, q2, q3);
@@ -560,6 +590,7 @@ trace_wq(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr, uin
             const unsigned b = __ballot_sync(0xffffffffu, has);
             if (b) {
                 // qn < 32 here (every iteration ends with qn < 32), so at most 63 entries are ever queued
+                WPT_CHECK(qn + (uint32_t)__popc(b) <= (uint32_t)kQueueCap, 0);
                 if (has)
                     ws.queue[qn + (uint32_t)__popc(b & ((1u << lane) - 1u))] = make_uint2((lane << 27) | tri0, (L << 16) | (cnt2 & 0xffffu));
                 qn += (uint32_t)__popc(b);

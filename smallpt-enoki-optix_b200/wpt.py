@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwpt.so")
+# WPT_LIB: another build of the same library (libwpt_checked.so, tests/test_gpu_checked.py)
+LIB_PATH = os.environ.get("WPT_LIB", os.path.join(_HERE, "libwpt.so"))
 WPT_MAX_DEPTH = 64
 
 
