@@ -372,6 +372,10 @@ def run_ours(args):
         traffic, traffic_src = traffic_per_launch(pst["segments"] / n_trace)
         shade_s = pst["ms_shade"] * 1e-3
         shaded = sum(pst["live"][:wave])           # segments that went through shade_kernel (the fused tail shades its own)
+        # algorithmic bytes of those launches: every segment reads its ray record and hit (40 + 16 B); only the paths that go
+        # on (the rays entering the next bounce) gather 48 B of attributes and write a 40 B record
+        cont = sum(pst["live"][j + 1] for j in range(wave) if j + 1 < depth)
+        shade_bytes = shaded * 56 + cont * 88
         roof = {"bound": "hbm", "kernel": "trace_wq", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "peak_source": which, "traffic": traffic, "traffic_source": traffic_src,
                 "traffic_note": "derived: dram__bytes per ray of the committed ncu --set full capture x this run's rays per launch",
@@ -384,10 +388,10 @@ def run_ours(args):
                 "trace_time_includes": "depth pre-pass, second traces and (fused tail) the in-kernel shading of bounces >= %d" % wave,
                 "share_of_step": {"raygen": pst["ms_raygen"] / pst["ms_total"], "trace": pst["ms_trace"] / pst["ms_total"],
                                   "shade": pst["ms_shade"] / pst["ms_total"]},
-                "shade": {"kernel": "shade_kernel", "bound": "hbm", "alg_bytes_per_ray": ab["shade"],
-                          "achieved": shaded * ab["shade"] / max(shade_s, 1e-9) / 1e9,
-                          "frac": shaded * ab["shade"] / max(shade_s, 1e-9) / 1e9 / peak, "segments": shaded,
-                          "ms": pst["ms_shade"]},
+                "shade": {"kernel": "shade_kernel", "bound": "hbm", "alg_bytes": "56 B per segment + 88 B per continuing path",
+                          "achieved": shade_bytes / max(shade_s, 1e-9) / 1e9,
+                          "frac": shade_bytes / max(shade_s, 1e-9) / 1e9 / peak, "segments": shaded, "continuing": cont,
+                          "ms": pst["ms_shade"], "ncu": "profiles/r2_stream_kernels_ncu.txt"},
                 "pipeline": {"alg_bytes_per_ray": ab["pipeline"],
                              "achieved": value / world * 1e6 * ab["pipeline"] / 1e9,
                              "frac": value / world * 1e6 * ab["pipeline"] / 1e9 / peak},
