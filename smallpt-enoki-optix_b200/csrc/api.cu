@@ -143,7 +143,8 @@ extern "C" void wpt_scene_destroy(wpt_scene *s)
     delete s;
 }
 
-extern "C" int wpt_scene_commit(wpt_scene *s, int device)
+// builder 0: SAH build on the host (bvh_build.cpp); 1: Morton-order LBVH on the device (lbvh_build.cu)
+static int scene_commit(wpt_scene *s, int device, int builder)
 {
     if (!s) return fail(WPT_E_INVALID, "wpt_scene_commit: null scene");
     int ndev = 0;
@@ -165,11 +166,22 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
 
     BuiltBvh b;
     const char *err = nullptr;
-    if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
-        return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
-    // the warp queue of trace_wq packs (owner lane << 27 | block index) into one word
-    if (!blocks_within_limit(b.blocks.size()))
-        return fail(WPT_E_LIMIT, "wpt_scene_commit: more than 2^27 BVH blocks (about 115 M triangles)");
+    if (builder == 0) {
+        if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
+            return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
+        // the warp queue of trace_wq packs (owner lane << 27 | block index) into one word
+        if (!blocks_within_limit(b.blocks.size()))
+            return fail(WPT_E_LIMIT, "wpt_scene_commit: more than 2^27 BVH blocks (about 115 M triangles)");
+    } else {
+        // the checks build_bvh7 makes on its input
+        const uint32_t n_pos = (uint32_t)(s->pos.size() / 3);
+        for (int32_t v : s->pidx)
+            if (v < 0 || (uint32_t)v >= n_pos) return fail(WPT_E_INVALID, "BVH build: position index out of range");
+        for (float x : s->pos)
+            if (!std::isfinite(x)) return fail(WPT_E_INVALID, "BVH build: non-finite vertex position");
+        if (!blocks_within_limit(2ull * s->n_tris + 2ull))
+            return fail(WPT_E_LIMIT, "wpt_scene_commit_lbvh: more than 2^27 BVH blocks");
+    }
 
     // per-ORIGINAL-triangle shading attributes: 3 vertex normals + material, one 48 B gather per hit
     std::vector<TriAttr48> attr(s->n_tris);
@@ -207,23 +219,43 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     WPT_CUDA(cudaGetDeviceProperties(&prop, device));
     s->device = device;
     s->num_sms = prop.multiProcessorCount;
-    WPT_CUDA(cudaMalloc(&s->d_blocks, b.blocks.size() * sizeof(Block64)));
+    if (builder == 0) WPT_CUDA(cudaMalloc(&s->d_blocks, b.blocks.size() * sizeof(Block64)));
     WPT_CUDA(cudaMalloc(&s->d_attr, attr.size() * sizeof(TriAttr48)));
     WPT_CUDA(cudaMalloc(&s->d_albedo, s->albedo.size() * sizeof(float)));
     WPT_CUDA(cudaMalloc(&s->d_cursor, kCursorRing * sizeof(uint32_t)));
-    WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
+    if (builder == 0) WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
-    WPT_CUDA(cudaMalloc(&s->d_level_nodes, b.level_nodes.size() * sizeof(uint32_t)));
+    if (builder == 0) WPT_CUDA(cudaMalloc(&s->d_level_nodes, b.level_nodes.size() * sizeof(uint32_t)));
     WPT_CUDA(cudaMalloc(&s->d_geo, geo.size()));
-    WPT_CUDA(cudaMemcpy(s->d_level_nodes, b.level_nodes.data(), b.level_nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    if (builder == 0) WPT_CUDA(cudaMemcpy(s->d_level_nodes, b.level_nodes.data(), b.level_nodes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_geo, geo.data(), geo.size(), cudaMemcpyHostToDevice));
-    s->level_begin = b.level_begin;
+    if (builder == 0) s->level_begin = b.level_begin;
     // vertex positions and index triplets: refit (csrc/refit.cu) and wpt_hit_attributes (geometry normal)
     WPT_CUDA(cudaMalloc(&s->d_pos, s->pos.size() * sizeof(float)));
     WPT_CUDA(cudaMalloc(&s->d_pidx, s->pidx.size() * sizeof(int32_t)));
     WPT_CUDA(cudaMemcpy(s->d_pos, s->pos.data(), s->pos.size() * sizeof(float), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_pidx, s->pidx.data(), s->pidx.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    uint32_t n_blocks = (uint32_t)b.blocks.size();
+    if (builder != 0) {
+        // device build: topology from the sorted Morton codes, then the geometry of every block (triangle operands,
+        // float boxes, quantised planes) by the refit kernels, deepest level first
+        const auto tb0 = std::chrono::steady_clock::now();
+        NvtxRange nvtx_lbvh("lbvh_build");
+        if (!lbvh_build_topology(s->d_pos, s->d_pidx, s->n_tris, &s->d_blocks, &n_blocks, &s->d_level_nodes, s->level_begin,
+                                 &b.n_nodes, &b.max_depth, &err, nullptr))
+        {
+            scene_free_device(s);
+            return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_CUDA, std::string("LBVH build: ") + err);
+        }
+        WPT_CUDA(cudaMalloc(&s->d_boxes, (size_t)n_blocks * 6 * sizeof(float)));
+        launch_refit(s->d_blocks, s->d_level_nodes, s->level_begin.data(), (uint32_t)s->level_begin.size() - 1, s->d_pos,
+                     s->d_pidx, s->d_boxes, s->d_attr, s->d_geo, nullptr);
+        WPT_CUDA(cudaDeviceSynchronize());
+        b.n_tris = s->n_tris;
+        b.sah_cost = 0.0;       // not evaluated for the device build
+        b.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tb0).count();
+    }
     if (!s->uvs.empty()) {
         WPT_CUDA(cudaMalloc(&s->d_uvs, s->uvs.size() * sizeof(float)));
         WPT_CUDA(cudaMalloc(&s->d_uvidx, s->uvidx.size() * sizeof(int32_t)));
@@ -263,7 +295,7 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     const double up_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 
     s->view.blocks = reinterpret_cast<const uint4 *>(s->d_blocks);
-    s->view.n_blocks = (uint32_t)b.blocks.size();
+    s->view.n_blocks = n_blocks;
     s->view.n_nodes = b.n_nodes;
     s->view.n_tris = b.n_tris;
     s->view.max_depth = b.max_depth;
@@ -280,6 +312,9 @@ extern "C" int wpt_scene_commit(wpt_scene *s, int device)
     s->committed = true;
     return WPT_OK;
 }
+
+extern "C" int wpt_scene_commit(wpt_scene *s, int device) { return scene_commit(s, device, 0); }
+extern "C" int wpt_scene_commit_lbvh(wpt_scene *s, int device) { return scene_commit(s, device, 1); }
 
 extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
 {

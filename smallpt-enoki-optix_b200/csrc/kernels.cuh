@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <vector>
 #include "bvh.h"
 #include "../../include/wpt.h"
 
@@ -109,6 +110,10 @@ void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cu
 void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
                   const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,
                   cudaStream_t st);
+// lbvh_build.cu: topology of a 7-wide tree built on the device (geometry is then written by launch_refit)
+bool lbvh_build_topology(const float *d_pos, const int32_t *d_pidx, uint32_t n_tris, Block64 **d_blocks_out,
+                         uint32_t *n_blocks_out, uint32_t **d_level_nodes_out, std::vector<uint32_t> &level_begin,
+                         uint32_t *n_nodes_out, uint32_t *max_depth_out, const char **err, cudaStream_t st);
 void launch_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out, cudaStream_t st);
 
 }  // namespace wpt

@@ -264,10 +264,14 @@ class Scene:
         _check(lib().wpt_scene_set_texture(self._h, C.c_uint32(material), C.c_void_p(img.ctypes.data),
                                            C.c_uint32(img.shape[1]), C.c_uint32(img.shape[0])))
 
-    def commit(self, device=0):
+    def commit(self, device=0, builder="sah"):
+        """builder "sah": host SAH build (default); "lbvh": Morton-order build on the device (wpt_scene_commit_lbvh)"""
         if not self._h:
             raise WptError(3, "Scene.commit: no mesh")
-        _check(lib().wpt_scene_commit(self._h, C.c_int(device)))
+        if builder == "lbvh":
+            _check(lib().wpt_scene_commit_lbvh(self._h, C.c_int(device)))
+        else:
+            _check(lib().wpt_scene_commit(self._h, C.c_int(device)))
         self.device = device
 
     def refit(self, positions):
@@ -509,11 +513,11 @@ class Fimage:
                                   C.c_void_p(b.ctypes.data), C.c_uint32(width), C.c_uint32(height)))
 
 
-def scene_from(sd, device=0):
+def scene_from(sd, device=0, builder="sah"):
     """SceneData (scenes.py) -> committed Scene"""
     s = Scene()
     s.add_triangle_mesh(sd.pos, sd.idx, sd.nrm, sd.nidx, sd.mat, sd.albedo)
-    s.commit(device)
+    s.commit(device, builder)
     return s
 
 
