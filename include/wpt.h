@@ -87,8 +87,8 @@ int  wpt_scene_commit(wpt_scene *s, int device);
 /* The same commit with the tree built ON THE DEVICE (the reference's own build is a device build
  * too: optixAccelBuild, src/accel/optix_backend.h:309-358): 63-bit Morton codes, radix sort, binary radix tree
  * (Karras 2012), bottom-up boxes, level-by-level collapse to 7-wide nodes with <= 3-triangle leaves, then the block
- * geometry by the refit kernels.  Milliseconds per million triangles instead of 0.3 s, for scenes whose topology
- * changes between frames; the trees are of lower quality than the host SAH builder's (traversal ~1.3-1.6x slower), hits
+ * geometry by the refit kernels.  10 ms per million triangles instead of 0.3 s, for scenes whose topology
+ * changes between frames; the trees are of lower quality than the host SAH builder's (traversal ~1.2x slower, measured), hits
  * are the same closest hits.  sah_cost is reported as 0 (not evaluated).  WPT_E_LIMIT if the tree is deeper than 32. */
 int  wpt_scene_commit_lbvh(wpt_scene *s, int device);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);

@@ -4,7 +4,8 @@
 // SURVEY §8(f) rank 4.  The reference builds its acceleration structure on the device too (optixAccelBuild inside
 // OptixBackend::set_triangles_soup, src/accel/optix_backend.h:283-364); the default builder of this library is the
 // host SAH builder (bvh_build.cpp: better trees, 0.3 s per million triangles); this one is for scenes whose topology
-// changes per frame (wpt_scene_commit_lbvh: a few milliseconds per million triangles, trees ~1.3-1.6x the SAH cost).
+// changes per frame (wpt_scene_commit_lbvh: 10 ms per million triangles on B200; traversal 1.2x slower than on the SAH
+// tree, profiles/r2_lbvh.txt).
 //
 // Steps (all kernels below; the radix sort is CUB's, library code outside the render path):
 //   1. per triangle: box, centroid -> 63-bit Morton code in the scene box          morton_kernel

@@ -19,7 +19,9 @@ name = sys.argv[1] if len(sys.argv) > 1 else "C3"
 grid = [tuple(int(x) for x in g.split(",")) for g in (sys.argv[2] if len(sys.argv) > 2 else "0,0,1,64").split(";") if g]
 gen, W, H, spp0, depth = scenes.CONFIGS[name]
 sd = gen()
-scene = wpt.scene_from(sd)
+builder = sys.argv[3] if len(sys.argv) > 3 else "sah"
+scene = wpt.scene_from(sd, builder=builder)
+print(json.dumps({"builder": builder, **{k: scene.stats()[k] for k in ("n_nodes", "max_depth", "build_ms", "sah_cost")}}), flush=True)
 cam = wpt.camera_from(sd)
 N = W * H
 film = torch.zeros(3, N, device="cuda")
