@@ -103,6 +103,9 @@ int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
  * next wpt_scene_commit, which reads the positions back and rejects non-finite ones. */
 int  wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions);
 int  wpt_scene_refit_device(wpt_scene *s, const float *d_positions, void *stream);
+/* After a refit: *non_finite = 1 if a NaN / Inf vertex reached the tree (the refit kernels raise a flag word; the tree
+ * is then undefined until the next commit).  Waits for `stream`. */
+int  wpt_scene_refit_status(const wpt_scene *s, int *non_finite, void *stream);
 void wpt_scene_destroy(wpt_scene *s);
 
 /* ------------------------------------------------------------------ OBJ / MTL ingestion

@@ -222,7 +222,7 @@ static int scene_commit(wpt_scene *s, int device, int builder)
     if (builder == 0) WPT_CUDA(cudaMalloc(&s->d_blocks, b.blocks.size() * sizeof(Block64)));
     WPT_CUDA(cudaMalloc(&s->d_attr, attr.size() * sizeof(TriAttr48)));
     WPT_CUDA(cudaMalloc(&s->d_albedo, s->albedo.size() * sizeof(float)));
-    WPT_CUDA(cudaMalloc(&s->d_cursor, kCursorRing * sizeof(uint32_t)));
+    WPT_CUDA(cudaMalloc(&s->d_cursor, (kCursorRing + 1) * sizeof(uint32_t)));   // + the refit flag word
     if (builder == 0) WPT_CUDA(cudaMemcpy(s->d_blocks, b.blocks.data(), b.blocks.size() * sizeof(Block64), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_attr, attr.data(), attr.size() * sizeof(TriAttr48), cudaMemcpyHostToDevice));
     WPT_CUDA(cudaMemcpy(s->d_albedo, s->albedo.data(), s->albedo.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -329,8 +329,11 @@ extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
 static int refit_common(wpt_scene *s, const float *d_positions, cudaStream_t st)
 {
     if (!s->d_boxes) WPT_CUDA(cudaMalloc(&s->d_boxes, (size_t)s->view.n_blocks * 6 * sizeof(float)));
+    // flag word: cursor slot kCursorRing (one past the ring) — set by the refit kernels on a non-finite vertex
+    uint32_t *flag = s->d_cursor + kCursorRing;
+    WPT_CUDA(cudaMemsetAsync(flag, 0, sizeof(uint32_t), st));
     launch_refit(s->d_blocks, s->d_level_nodes, s->level_begin.data(), (uint32_t)s->level_begin.size() - 1, d_positions,
-                 s->d_pidx, s->d_boxes, s->d_attr, s->d_geo, st);
+                 s->d_pidx, s->d_boxes, s->d_attr, s->d_geo, st, flag);
     WPT_CUDA(cudaGetLastError());
     return WPT_OK;
 }
@@ -345,6 +348,20 @@ extern "C" int wpt_scene_refit_device(wpt_scene *s, const float *d_positions, vo
         WPT_CUDA(cudaMemcpyAsync(s->d_pos, d_positions, s->pos.size() * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     s->pos_on_device_newer = true;
     return refit_common(s, s->d_pos, (cudaStream_t)stream);
+}
+
+// Result of the last refit: 0 = fine, 1 = a non-finite vertex reached the tree (the device path cannot validate its
+// input beforehand).  Waits for `stream`.
+extern "C" int wpt_scene_refit_status(const wpt_scene *s, int *non_finite, void *stream)
+{
+    if (!s || !non_finite) return fail(WPT_E_INVALID, "wpt_scene_refit_status: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_scene_refit_status: scene not committed");
+    WPT_CUDA(cudaSetDevice(s->device));
+    uint32_t f = 0;
+    WPT_CUDA(cudaMemcpyAsync(&f, s->d_cursor + kCursorRing, sizeof f, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    WPT_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    *non_finite = f ? 1 : 0;
+    return WPT_OK;
 }
 
 extern "C" int wpt_scene_refit(wpt_scene *s, const float *positions, uint32_t n_positions)

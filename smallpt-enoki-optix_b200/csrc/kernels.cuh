@@ -109,7 +109,7 @@ void launch_shade_streams(uint32_t n, const float *const o[3], const float *cons
 void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st);
 void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
                   const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,
-                  cudaStream_t st);
+                  cudaStream_t st, uint32_t *bad_flag = nullptr);
 // lbvh_build.cu: topology of a 7-wide tree built on the device (geometry is then written by launch_refit)
 bool lbvh_build_topology(const float *d_pos, const int32_t *d_pidx, uint32_t n_tris, Block64 **d_blocks_out,
                          uint32_t *n_blocks_out, uint32_t **d_level_nodes_out, std::vector<uint32_t> &level_begin,

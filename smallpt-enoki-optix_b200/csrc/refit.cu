@@ -31,7 +31,7 @@ __device__ __forceinline__ int exp_for_extent_dev(float extent, float maxabs)
 __global__ void __launch_bounds__(128)
 refit_level_kernel(Block64 *__restrict__ blocks, const uint32_t *__restrict__ level_nodes, uint32_t count,
                    const float *__restrict__ pos, const int32_t *__restrict__ pidx, float *__restrict__ boxes,
-                   TriAttr48 *__restrict__ attr, const uint8_t *__restrict__ geo_normal)
+                   TriAttr48 *__restrict__ attr, const uint8_t *__restrict__ geo_normal, uint32_t *__restrict__ bad_flag)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
@@ -85,6 +85,22 @@ refit_level_kernel(Block64 *__restrict__ blocks, const uint32_t *__restrict__ le
             for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], clo[s][k]); hi[k] = fmaxf(hi[k], chi[s][k]); }
     }
     for (int k = 0; k < 3; k++) { boxes[6 * (size_t)nb + k] = lo[k]; boxes[6 * (size_t)nb + 3 + k] = hi[k]; }
+    // device-side positions cannot be validated by the host: a NaN / Inf vertex shows up here as a non-finite box
+    // (fminf / fmaxf drop NaNs, so the triangle operands are checked as well) and raises the scene's flag word
+    if (bad_flag) {
+        bool ok = true;
+        for (int k = 0; k < 3; k++) ok = ok && isfinite(lo[k]) && isfinite(hi[k]);
+        uint32_t off = 0;
+        for (int sl = 0; sl < kWidth && ok; sl++) {
+            const uint32_t cnt = ((imask >> sl) & 1u) ? 0u : ((cnt2 >> (2 * sl)) & 3u);
+            for (uint32_t t = 0; t < cnt && ok; t++) {
+                const Tri64 &tr = blocks[node.base + n_int + off + t].tri;
+                for (int k = 0; k < 3; k++) ok = ok && isfinite(tr.v0[k]) && isfinite(tr.e1[k]) && isfinite(tr.e2[k]);
+            }
+            off += cnt;
+        }
+        if (!ok) atomicOr(bad_flag, 1u);
+    }
 
     uint8_t *plo[3] = {node.xlo, node.ylo, node.zlo}, *phi[3] = {node.xhi, node.yhi, node.zhi};
     int eb[3];
@@ -113,13 +129,13 @@ refit_level_kernel(Block64 *__restrict__ blocks, const uint32_t *__restrict__ le
 
 void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
                   const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,
-                  cudaStream_t st)
+                  cudaStream_t st, uint32_t *bad_flag)
 {
     for (uint32_t d = n_levels; d-- > 0;) {
         const uint32_t first = level_begin_host[d], count = level_begin_host[d + 1] - first;
         if (!count) continue;
         refit_level_kernel<<<(count + 127) / 128, 128, 0, st>>>(blocks, level_nodes + first, count, pos, pidx, boxes,
-                                                                attr, geo_normal);
+                                                                attr, geo_normal, bad_flag);
     }
 }
 

@@ -284,6 +284,12 @@ class Scene:
             assert positions.is_cuda and positions.is_contiguous()
             _check(lib().wpt_scene_refit_device(self._h, C.c_void_p(positions.data_ptr()), _stream_handle(None)))
 
+    def refit_status(self):
+        """True if the last refit saw a non-finite vertex (wpt_scene_refit_status; synchronises)"""
+        f = C.c_int(0)
+        _check(lib().wpt_scene_refit_status(self._h, C.byref(f), _stream_handle(None)))
+        return bool(f.value)
+
     def stats(self):
         s = BvhStats()
         _check(lib().wpt_scene_stats(self._h, C.byref(s)))

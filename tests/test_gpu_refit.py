@@ -92,3 +92,24 @@ def test_refit_errors():
     bad = sd.pos.copy(); bad[0, 0] = np.nan
     with pytest.raises(wpt.WptError):
         s.refit(bad)
+
+
+def test_device_refit_flags_non_finite_vertices():
+    """wpt_scene_refit_device cannot validate device-side positions on the host; the refit kernels raise a
+    flag word instead (wpt_scene_refit_status), and the next commit (which reads the positions back) refuses them."""
+    import torch
+    import wpt
+    sd = scenes.cornell(8)
+    s = wpt.scene_from(sd)
+    good = torch.from_numpy(sd.pos.reshape(-1).copy()).cuda()
+    s.refit(good)
+    assert s.refit_status() is False
+    for bad_value in (float("nan"), float("inf")):
+        bad = good.clone()
+        bad[3 * 17 + 1] = bad_value
+        s.refit(bad)
+        assert s.refit_status() is True
+        with pytest.raises(wpt.WptError):
+            s.commit(0)                               # reads the device-side positions back: non-finite -> refused
+        s.refit(good)
+        assert s.refit_status() is False
