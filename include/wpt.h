@@ -224,7 +224,8 @@ int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
 /* Sharded depth pre-pass for a frame split over n_ranks GPUs (wpt_film_reduce below): every rank needs the same seeds,
  * so instead of all of them repeating the whole one-ray-per-pixel pre-pass, rank g traces 1/n_ranks of it and the hit
  * distances are all-gathered on `nccl_comm` (ncclAllGather, W*H floats in total) inside wpt_render, on its stream.
- * EVERY rank of the communicator must then call wpt_render for every frame (it is a collective).  The seeds, hence
+ * EVERY rank of the communicator must then call wpt_render for every frame (it is a collective), with the same camera
+ * kind, tmax and depth-seeding setting; the pre-pass then runs whatever the rank's own sample count (no >= 8 rule).  The seeds, hence
  * the frame, are bit-identical to the unsharded pre-pass.  nccl_comm = NULL or n_ranks <= 1 switches it off. */
 int  wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, int rank, int n_ranks);
 /* Fused tail: bounces >= first_bounce of every pass run in ONE launch of the traversal kernel with the shading step

@@ -842,11 +842,14 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
     // the few rays that find nothing inside it are traced a second time with the full interval.  Pinhole cameras only
     // (every ray of a pixel leaves the same point), the reference's unbounded tmax (src/ray.h:16) only, and only
     // where the pre-pass is a small fraction of the frame.
-    const bool seeded = r->seeding && cam->lens_radius == 0.0f && cfg->spp_count >= 8 && cfg->tmax >= 1e20f;
+    // With a sharded pre-pass the decision must be the same on every rank (the all-gather is a collective): it then does
+    // not depend on this rank's own sample count (ranks of an uneven split may hold 7 and 8 samples).
+    const bool shard_on = r->shard_comm && r->shard_n > 1 && r->tlane;
+    const bool seeded = r->seeding && cam->lens_radius == 0.0f && cfg->tmax >= 1e20f && (cfg->spp_count >= 8 || shard_on);
     if (seeded) {
         // every rank of a sharded frame needs the same seeds: with wpt_renderer_set_depth_shard each rank traces 1/n of the
         // pixel-centre rays and the hit distances are all-gathered, instead of every rank repeating the whole pre-pass
-        const bool shard = r->shard_comm && r->shard_n > 1 && r->tlane;
+        const bool shard = shard_on;
         const uint32_t chunk = shard ? (N + (uint32_t)r->shard_n - 1) / (uint32_t)r->shard_n : N;
         const uint32_t lane0 = shard ? std::min(N, (uint32_t)r->shard_rank * chunk) : 0u;
         const uint32_t lanes = shard ? std::min(N - lane0, chunk) : N;
