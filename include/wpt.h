@@ -91,6 +91,12 @@ int  wpt_scene_commit(wpt_scene *s, int device);
  * changes between frames; the trees are of lower quality than the host SAH builder's (traversal ~1.2x slower, measured), hits
  * are the same closest hits.  sah_cost is reported as 0 (not evaluated).  WPT_E_LIMIT if the tree is deeper than 32. */
 int  wpt_scene_commit_lbvh(wpt_scene *s, int device);
+/* wpt_scene_commit with the host-built tree kept in a file: if `cache_path` holds the tree of exactly this mesh (hash of
+ * positions and indices, library version) it is loaded instead of built, otherwise the tree is built and the file written
+ * (atomically: temp file + rename).  For the G ranks of a multi-GPU job on one box (one process per GPU, same mesh): one
+ * rank commits first, the others then load — one SAH build (C4: 3.5-4.7 s) instead of G.  *from_cache (optional) = 1 if
+ * the tree was loaded.  A cache that cannot be read or written is not an error: the tree is built. */
+int  wpt_scene_commit_cached(wpt_scene *s, int device, const char *cache_path, int *from_cache);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
 /* Moved vertices, same topology: bottom-up refit of the node boxes and rewrite of the triangle blocks ON THE
  * DEVICE, one launch per tree level (the reference rebuilds its GAS from scratch,

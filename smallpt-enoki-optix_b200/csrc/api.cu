@@ -4,6 +4,8 @@
 #include <nccl.h>   // types and prototypes only: the library is bound with dlopen (wpt_film_reduce)
 #include <nvtx3/nvToolsExt.h>
 
+#include <unistd.h>
+
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -68,6 +70,7 @@ struct wpt_scene {
     MatTex *d_mattex = nullptr;
     float2 *d_triuv = nullptr;
     TexArgs tex{nullptr, nullptr, nullptr};
+    bool tree_from_cache = false;
     bool pos_on_device_newer = false;   // wpt_scene_refit_device moved the vertices: the next commit reads them back
     // device
     int device = -1, num_sms = 0;
@@ -143,8 +146,62 @@ extern "C" void wpt_scene_destroy(wpt_scene *s)
     delete s;
 }
 
+// ---- tree cache (wpt_scene_commit_cached): the host-built tree of a mesh as one file, so that the G ranks of a
+// multi-GPU job (one process per GPU, same mesh) build it once instead of G times
+namespace {
+struct TreeFileHeader {
+    uint64_t magic, mesh_hash;
+    uint32_t version, n_tris, n_nodes, max_depth;
+    uint64_t n_blocks, n_level_nodes, n_level_begin;
+    double sah_cost, build_ms;
+};
+constexpr uint64_t kTreeMagic = 0x3154504257ull;   // "WBPT1"
+uint64_t fnv1a(const void *p, size_t n, uint64_t h)
+{
+    const uint8_t *b = static_cast<const uint8_t *>(p);
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 0x100000001b3ull; }
+    return h;
+}
+uint64_t mesh_hash(const wpt_scene *s)
+{
+    uint64_t h = 0xcbf29ce484222325ull;
+    h = fnv1a(s->pos.data(), s->pos.size() * sizeof(float), h);
+    return fnv1a(s->pidx.data(), s->pidx.size() * sizeof(int32_t), h);
+}
+bool tree_load(const char *path, uint64_t hash, uint32_t n_tris, BuiltBvh &b)
+{
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return false;
+    TreeFileHeader h;
+    bool ok = std::fread(&h, sizeof h, 1, f) == 1 && h.magic == kTreeMagic && h.version == WPT_VERSION && h.mesh_hash == hash &&
+              h.n_tris == n_tris && h.n_blocks <= kMaxBlocks && h.n_level_nodes <= h.n_blocks && h.n_level_begin <= 64;
+    if (ok) {
+        b.blocks.resize(h.n_blocks); b.level_nodes.resize(h.n_level_nodes); b.level_begin.resize(h.n_level_begin);
+        ok = std::fread(b.blocks.data(), sizeof(Block64), h.n_blocks, f) == h.n_blocks &&
+             std::fread(b.level_nodes.data(), sizeof(uint32_t), h.n_level_nodes, f) == h.n_level_nodes &&
+             std::fread(b.level_begin.data(), sizeof(uint32_t), h.n_level_begin, f) == h.n_level_begin;
+        b.n_nodes = h.n_nodes; b.n_tris = h.n_tris; b.max_depth = h.max_depth; b.sah_cost = h.sah_cost; b.build_ms = h.build_ms;
+    }
+    std::fclose(f);
+    return ok;
+}
+void tree_store(const char *path, uint64_t hash, const BuiltBvh &b)
+{
+    const std::string tmp = std::string(path) + ".tmp" + std::to_string((unsigned long long)hash & 0xffff) + std::to_string((long)getpid());
+    FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return;                                   // a cache that cannot be written is not an error
+    TreeFileHeader h{kTreeMagic, hash, WPT_VERSION, b.n_tris, b.n_nodes, b.max_depth, b.blocks.size(), b.level_nodes.size(),
+                     b.level_begin.size(), b.sah_cost, b.build_ms};
+    const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(b.blocks.data(), sizeof(Block64), b.blocks.size(), f) == b.blocks.size() &&
+                    std::fwrite(b.level_nodes.data(), sizeof(uint32_t), b.level_nodes.size(), f) == b.level_nodes.size() &&
+                    std::fwrite(b.level_begin.data(), sizeof(uint32_t), b.level_begin.size(), f) == b.level_begin.size();
+    std::fclose(f);
+    if (ok) std::rename(tmp.c_str(), path); else std::remove(tmp.c_str());     // atomic: readers see a whole file or none
+}
+}  // namespace
+
 // builder 0: SAH build on the host (bvh_build.cpp); 1: Morton-order LBVH on the device (lbvh_build.cu)
-static int scene_commit(wpt_scene *s, int device, int builder)
+static int scene_commit(wpt_scene *s, int device, int builder, const char *cache_path = nullptr)
 {
     if (!s) return fail(WPT_E_INVALID, "wpt_scene_commit: null scene");
     int ndev = 0;
@@ -167,8 +224,14 @@ static int scene_commit(wpt_scene *s, int device, int builder)
     BuiltBvh b;
     const char *err = nullptr;
     if (builder == 0) {
-        if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
-            return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
+        const uint64_t hash = cache_path ? mesh_hash(s) : 0;
+        const bool cached = cache_path && tree_load(cache_path, hash, s->n_tris, b);
+        s->tree_from_cache = cached;
+        if (!cached) {
+            if (!build_bvh7(s->pos.data(), (uint32_t)(s->pos.size() / 3), s->pidx.data(), s->n_tris, b, &err))
+                return fail(std::strstr(err, "deeper") ? WPT_E_LIMIT : WPT_E_INVALID, std::string("BVH build: ") + err);
+            if (cache_path) tree_store(cache_path, hash, b);
+        }
         // the warp queue of trace_wq packs (owner lane << 27 | block index) into one word
         if (!blocks_within_limit(b.blocks.size()))
             return fail(WPT_E_LIMIT, "wpt_scene_commit: more than 2^27 BVH blocks (about 115 M triangles)");
@@ -315,6 +378,13 @@ static int scene_commit(wpt_scene *s, int device, int builder)
 
 extern "C" int wpt_scene_commit(wpt_scene *s, int device) { return scene_commit(s, device, 0); }
 extern "C" int wpt_scene_commit_lbvh(wpt_scene *s, int device) { return scene_commit(s, device, 1); }
+extern "C" int wpt_scene_commit_cached(wpt_scene *s, int device, const char *cache_path, int *from_cache)
+{
+    if (!cache_path) return fail(WPT_E_INVALID, "wpt_scene_commit_cached: null path");
+    const int rc = scene_commit(s, device, 0, cache_path);
+    if (rc == WPT_OK && from_cache) *from_cache = s->tree_from_cache ? 1 : 0;
+    return rc;
+}
 
 extern "C" int wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out)
 {

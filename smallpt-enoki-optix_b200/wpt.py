@@ -264,11 +264,16 @@ class Scene:
         _check(lib().wpt_scene_set_texture(self._h, C.c_uint32(material), C.c_void_p(img.ctypes.data),
                                            C.c_uint32(img.shape[1]), C.c_uint32(img.shape[0])))
 
-    def commit(self, device=0, builder="sah"):
+    def commit(self, device=0, builder="sah", cache_path=None):
         """builder "sah": host SAH build (default); "lbvh": Morton-order build on the device (wpt_scene_commit_lbvh)"""
         if not self._h:
             raise WptError(3, "Scene.commit: no mesh")
-        if builder == "lbvh":
+        self.from_cache = False
+        if cache_path is not None:
+            f = C.c_int(0)
+            _check(lib().wpt_scene_commit_cached(self._h, C.c_int(device), str(cache_path).encode(), C.byref(f)))
+            self.from_cache = bool(f.value)
+        elif builder == "lbvh":
             _check(lib().wpt_scene_commit_lbvh(self._h, C.c_int(device)))
         else:
             _check(lib().wpt_scene_commit(self._h, C.c_int(device)))
@@ -519,11 +524,11 @@ class Fimage:
                                   C.c_void_p(b.ctypes.data), C.c_uint32(width), C.c_uint32(height)))
 
 
-def scene_from(sd, device=0, builder="sah"):
+def scene_from(sd, device=0, builder="sah", cache_path=None):
     """SceneData (scenes.py) -> committed Scene"""
     s = Scene()
     s.add_triangle_mesh(sd.pos, sd.idx, sd.nrm, sd.nidx, sd.mat, sd.albedo)
-    s.commit(device, builder)
+    s.commit(device, builder, cache_path)
     return s
 
 

@@ -384,3 +384,33 @@ def test_image_textures_bilinear_eval_vs_oracle():
     s1.commit(0)
     f1, _ = wpt.Renderer(s1, W, H, 4).render_host(wpt.camera_from(sd), 0, 8, 5, seed=4)
     assert np.allclose(f1, pfilm, atol=2e-6)
+
+
+def test_commit_cached_shares_one_host_build(tmp_path):
+    """wpt_scene_commit_cached: the first commit builds and writes the tree file, the second loads it (same hits, same
+    stats); another mesh or a damaged file is rebuilt, never trusted."""
+    import torch
+    import wpt
+    sd = scenes.knob(100, 40)
+    path = tmp_path / "tree.bin"
+    a = wpt.scene_from(sd, cache_path=path)
+    assert a.from_cache is False and path.exists()
+    b = wpt.scene_from(sd, cache_path=path)
+    assert b.from_cache is True
+    sa, sb = a.stats(), b.stats()
+    assert all(sa[k] == sb[k] for k in ("n_nodes", "max_depth", "sah_cost", "n_leaf_slots"))
+    o, d = util.random_rays(sd, 100_000, seed=6)
+    ot, dt = _streams(torch, o, d)
+    for x, y in zip(a.intersect(ot, dt), b.intersect(ot, dt)):
+        assert torch.equal(torch.nan_to_num(x), torch.nan_to_num(y))
+    r = wpt.Renderer(b, 64, 64, 2)
+    film, st = r.render_host(wpt.camera_from(sd), 0, 4, 4, seed=1)
+    assert st["segments"] > 0                                   # refit levels etc. came along: the renderer works
+    b.refit(sd.pos)                                             # and so does the refit (level lists from the file)
+    other = scenes.knob(100, 41)
+    c = wpt.scene_from(other, cache_path=path)                  # different mesh: hash mismatch -> rebuilt and rewritten
+    assert c.from_cache is False
+    raw = bytearray(path.read_bytes()); raw[8] ^= 0xFF
+    path.write_bytes(bytes(raw))                                # damaged header
+    e = wpt.scene_from(other, cache_path=path)
+    assert e.from_cache is False and wpt.scene_from(other, cache_path=path).from_cache is True
