@@ -118,6 +118,8 @@ def test_c4_ten_million_triangles():
         films.append((f, s["segments"]))
         r.close()
     assert films[0][1] == films[1][1] and torch.equal(films[0][0], films[1][0])
+    # and the 3-sigma image of the 10 M-triangle scene against the oracle on Embree (1080p, 8 spp: seconds on the host)
+    _three_sigma_image(sd, scene, 1920, 1080, 8, depth, "C4")
 
 
 # ---------------------------------------------------------------- round 2: every BASELINE config at its configured size
