@@ -80,6 +80,18 @@ def traffic_per_launch(rays_per_launch):
     return None, None
 
 
+def ncu_counters():
+    """the binding-limit counters of the dominant kernel from the newest committed ncu summary (a profile run is never
+    a bench value; these are attached so that the line shows WHICH bound binds, SURVEY §8d's honesty note)"""
+    import glob
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_trace_counters.json")), reverse=True):
+        try:
+            return json.load(open(f))
+        except Exception:
+            continue
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -391,6 +403,7 @@ def run_ours(args):
                 "algorithmic_yardstick": True,
                 "binding_limit": "instruction issue + L1 data-stage wavefronts (ncu, profiles/); the BVH is L2 resident, so "
                                  "`achieved` counts ALGORITHMIC bytes (SURVEY §8d), not DRAM traffic",
+                "ncu_counters": ncu_counters(),
                 "alg_bytes_per_ray": ab["trace"], "rays_per_launch": pst["segments"] / n_trace,
                 "avg_launch_ms": pst["ms_trace"] / n_trace, "launches": n_trace,
                 "trace_mrays_s": pst["segments"] / trace_s / 1e6,
