@@ -12,6 +12,7 @@
 #include "kernels.cuh"
 #include "shade_core.h"
 #include "trace_core.h"
+#include <type_traits>
 
 namespace wpt {
 
@@ -679,6 +680,20 @@ static void launch_trace_any(const BvhView &bvh, const IO &io, const uint32_t *n
         if (tune.variant == 2) {
             auto kern = trace_persistent<IO, 20>;
             kern<<<(uint32_t)(num_sms * ctas_per_sm(kern, tune)), kTraceBlock, 0, st>>>(bvh, io, n_ptr, n_static, cursor, live_acc);
+            return;
+        }
+    }
+    // 30..33: experiments on the seeded camera rays only (QueueIOT<1>); every other source runs the default
+    if (tune.variant >= 30 && tune.variant <= 33) {
+        if constexpr (std::is_same<IO, QueueIOT<1>>::value) {
+            switch (tune.variant) {
+            case 30: launch_wq<IO, 24, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); return;
+            case 31: launch_wq<IO, 28, 8, 1>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); return;
+            case 32: launch_wq<IO, 20, 8, 0>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); return;
+            default: launch_wq<IO, 24, 8, 0>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st); return;
+            }
+        } else {
+            launch_wq<IO, kDefaultThresh, 8, kDefaultFlush>(bvh, io, n_ptr, n_static, cursor, live_acc, num_sms, tune, st);
             return;
         }
     }
