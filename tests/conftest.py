@@ -49,3 +49,21 @@ def hosttest():
     import ctypes as C
     # WPT_HOSTTEST_LIB: tools/sanitize.sh points this at the ASan/UBSan build
     return C.CDLL(os.environ.get("WPT_HOSTTEST_LIB", os.path.join(PKG, "libwpt_hosttest.so")))
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """WPT_LIB=.../libwpt_checked.so python -m pytest tests -m gpu: the whole GPU suite on the self-checking build —
+    at the end every invariant counter of the traversal kernels must still be zero (tests/test_gpu_checked.py does this
+    for tools/sanitize_target.py; this hook extends it to everything the suite launched in this process)."""
+    if "checked" not in os.environ.get("WPT_LIB", ""):
+        return
+    try:
+        import ctypes as C
+        import wpt
+        out = (C.c_uint32 * 8)()
+        rc = wpt.lib().wpt_debug_check_failures(out, C.c_int(0))
+        print("\nWPT_CHECKS counters after the session:", "unavailable" if rc else list(out))
+        if rc == 0 and any(out):
+            session.exitstatus = 1
+    except Exception as e:          # no device / library: nothing to report
+        print("\nWPT_CHECKS counters: not read (%s)" % e)
