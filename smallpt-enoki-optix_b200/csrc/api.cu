@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -647,8 +648,10 @@ struct NcclApi {
 };
 }  // namespace
 static NcclApi g_nccl;
+static std::mutex g_nccl_mutex;
 static int nccl_load()
 {
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
     if (g_nccl.lib) return WPT_OK;
     void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
@@ -699,6 +702,7 @@ struct wpt_renderer {
     void *shard_comm = nullptr;
     int shard_rank = 0, shard_n = 1;
     float *tlane = nullptr;
+    uint64_t tlane_floats = 0;
     // fused tail (wpt_renderer_set_tail): bounces >= tail_from of a pass run in ONE launch of trace_wq<TailIO>
     int tail_from = kDefaultTailFrom, tail_used = -1;
     // overlap mode (wpt_renderer_set_tuning, third knob): a second set of queues on its own stream; passes
@@ -803,10 +807,13 @@ extern "C" int wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, in
     if (!nccl_comm || n_ranks <= 1) { r->shard_comm = nullptr; r->shard_rank = 0; r->shard_n = 1; return WPT_OK; }
     if (rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_renderer_set_depth_shard: bad rank");
     if (int rc = nccl_load()) return rc;
-    if (!r->tlane) {
-        const uint64_t N = (uint64_t)r->W * r->H, chunk = (N + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+    const uint64_t N = (uint64_t)r->W * r->H, chunk = (N + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+    if (!r->tlane || r->tlane_floats < chunk * (uint64_t)n_ranks) {
         WPT_CUDA(cudaSetDevice(r->scene->device));
+        cudaFree(r->tlane);
+        r->tlane = nullptr;
         WPT_CUDA(cudaMalloc(&r->tlane, sizeof(float) * chunk * (uint64_t)n_ranks));
+        r->tlane_floats = chunk * (uint64_t)n_ranks;
     }
     r->shard_comm = nccl_comm; r->shard_rank = rank; r->shard_n = n_ranks;
     return WPT_OK;

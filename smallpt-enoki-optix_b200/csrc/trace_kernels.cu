@@ -634,18 +634,23 @@ trace_simple(const BvhView bvh, const IO io, const uint32_t *__restrict__ n_ptr,
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-// CTAs per SM of a persistent kernel: the occupancy calculator's answer, cached per (kernel, device)
+// CTAs per SM of a persistent kernel: the occupancy calculator's answer, cached per (kernel instantiation, device) —
+// instantiations differ in shared memory (stack rows) and so in occupancy, hence the key is the function pointer
 template <class K>
 static int ctas_per_sm(K kern, const TraceTuning &tune)
 {
     if (tune.ctas_per_sm > 0) return tune.ctas_per_sm;
-    static int cached[64] = {0};
+    struct Entry { const void *fn; int dev, ctas; };
+    static thread_local Entry cache[64];
+    static thread_local int n_cached = 0;
     int dev = 0;
     cudaGetDevice(&dev);
-    int &c = cached[dev & 63];
-    if (c <= 0) {
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, kern, kTraceBlock, 0) != cudaSuccess || c <= 0) c = 4;
-    }
+    const void *fn = reinterpret_cast<const void *>(kern);
+    for (int i = 0; i < n_cached; i++)
+        if (cache[i].fn == fn && cache[i].dev == dev) return cache[i].ctas;
+    int c = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, kern, kTraceBlock, 0) != cudaSuccess || c <= 0) c = 4;
+    if (n_cached < 64) cache[n_cached++] = Entry{fn, dev, c};
     return c;
 }
 
