@@ -162,6 +162,34 @@ int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t
 int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
                        uint32_t n, const wpt_hit_streams *hits);
 
+/* wpt_intersect_host without a single allocation.  No counterpart in the reference (its Enoki arrays allocate on every
+ * bounce, src/ray.h:20-26); it exists for hosts that have to keep cudaMalloc out of their per-bounce loop:
+ *   - a plugin inside an application whose own pool allocator has already claimed the whole GPU (Enoki's and
+ *     PyTorch's caching allocators do): a raw cudaMalloc for staging then fails with out-of-memory although the
+ *     application has plenty of room in its pool;
+ *   - a frame loop that cannot afford cudaMalloc / cudaFree, which wait for the whole device and so stall every
+ *     other stream of the process once per call;
+ *   - a thread working while another thread of the process records a CUDA graph in the default (global) capture
+ *     mode, where cudaMalloc from any thread breaks the recording.
+ * Same arguments, contract and results as wpt_intersect_host (HOST buffers in and out, bit-identical hits), plus the
+ * stream the copies and the kernel are queued on (NULL = default stream); it returns after that stream has drained.
+ * The device-side staging wpt_intersect_host allocates per call (eight ray streams, four result streams, the mask and
+ * the kernel's ray-fetch counter) lives in a fixed area inside the library image instead:
+ *   - it holds WPT_STATIC_MAX_RAYS rays; a larger n is refused with WPT_E_LIMIT and nothing is done — split the batch;
+ *   - it costs 12.3 MiB of device memory on every GPU that loads libwpt.so, from the load to the end of the process,
+ *     whether this entry point is ever called or not;
+ *   - there is ONE area per GPU and process, and it is not locked: two calls on the same GPU whose work overlaps there
+ *     (two threads, two streams) overwrite each other's rays and results.  Run them one after the other;
+ *   - the area keeps what the last call left in it.  The call zeroes the counter the kernel starts from and uploads
+ *     the caller's result arrays first, so masked-out and missed lanes come back exactly as the caller passed them;
+ *   - the first call on each GPU asks the runtime where that GPU's copy of the area is (cudaGetSymbolAddress) and
+ *     remembers it; make that first call at set-up, before any stream capture begins in the process.
+ * The scene itself is still allocated by wpt_scene_commit at load time; this call, like wpt_intersect, allocates
+ * nothing, on the device or through any library. */
+#define WPT_STATIC_MAX_RAYS (1u << 18)
+int wpt_intersect_host_static(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask,
+                              uint32_t mask_size, uint32_t n, const wpt_hit_streams *hits, void *stream);
+
 /* ------------------------------------------------------------------ derived hit attributes
  * What OptixBackend::intersect returns WITH the hit (src/accel/optix_backend.h:463-486, TriangleHitInfo :99-134) and
  * Scene::intersect turns into an Interaction (src/main.cpp:320-340): position o + t d, geometry normal

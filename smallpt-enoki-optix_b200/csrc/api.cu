@@ -599,6 +599,100 @@ extern "C" int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *ray
 }
 
 // ------------------------------------------------------------------------------------------------
+// wpt_intersect_host_static: wpt_intersect_host for callers that must not allocate (include/wpt.h).  The device-side
+// staging that wpt_intersect_host cudaMallocs per call — 8 ray streams, 4 hit streams, the mask, the kernel's ray-fetch
+// cursor — is carved out of ONE array that is part of the library image.  Every device that loads libwpt.so holds a
+// copy of it (about 12.3 MiB) until the process exits.
+constexpr uint32_t kStaticMaxRays = WPT_STATIC_MAX_RAYS;
+constexpr size_t kStaticCursorBytes = 256;                                    // keeps the streams behind it 256-aligned
+constexpr size_t kStaticStreamBytes = sizeof(float) * (size_t)kStaticMaxRays; // one f32 / i32 stream at full size
+constexpr size_t kStaticBytes = kStaticCursorBytes + 12 * kStaticStreamBytes + kStaticMaxRays /* mask */;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address the GPU understands: the device
+// address has to be asked for, per device (each one has its own copy), with that device current.
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char *g_static_base[kStaticMaxDevices] = {};
+
+// `device` must be current.  Looks the address up on the first call for that device and remembers it.
+static int static_scratch_base(int device, unsigned char **out)
+{
+    if (device < 0 || device >= kStaticMaxDevices)
+        return fail(WPT_E_LIMIT, "wpt_intersect_host_static: device ordinal beyond " + std::to_string(kStaticMaxDevices - 1));
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_base[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(WPT_E_CUDA, std::string("wpt_intersect_host_static: cudaGetSymbolAddress(g_static_scratch): ") +
+                                        cudaGetErrorString(e));
+        g_static_base[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_base[device];
+    return WPT_OK;
+}
+
+extern "C" int wpt_intersect_host_static(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask,
+                                         uint32_t mask_size, uint32_t n, const wpt_hit_streams *hits, void *stream)
+{
+    if (!s || !rays || !hits) return fail(WPT_E_INVALID, "wpt_intersect_host_static: null argument");
+    if (!s->committed) return fail(WPT_E_STATE, "wpt_intersect_host_static: scene not committed");
+    if (n > kStaticMaxRays)
+        return fail(WPT_E_LIMIT, "wpt_intersect_host_static: " + std::to_string(n) + " rays in one call, the built-in staging area holds " +
+                                     std::to_string(kStaticMaxRays) + " (WPT_STATIC_MAX_RAYS): split the batch or use wpt_intersect_host");
+    if (n == 0) return WPT_OK;
+    if (!rays->ox || !rays->oy || !rays->oz || !rays->dx || !rays->dy || !rays->dz || !hits->tri_id || !hits->t ||
+        !hits->u || !hits->v)
+        return fail(WPT_E_INVALID, "wpt_intersect_host_static: null stream");
+    if (mask && mask_size != 1 && mask_size != n)
+        return fail(WPT_E_INVALID, "wpt_intersect_host_static: mask_size must be 1 or n");
+    cudaStream_t st = (cudaStream_t)stream;
+    WPT_CUDA(cudaSetDevice(s->device));
+    unsigned char *base = nullptr;
+    if (int rc = static_scratch_base(s->device, &base)) return rc;
+
+    // layout: [cursor | 12 streams of kStaticMaxRays 4-byte items | mask]
+    uint32_t *cursor = reinterpret_cast<uint32_t *>(base);
+    float *d = reinterpret_cast<float *>(base + kStaticCursorBytes);
+    uint8_t *dm = base + kStaticCursorBytes + 12 * kStaticStreamBytes;
+    auto slot = [&](int k) { return d + (size_t)k * kStaticMaxRays; };
+    const size_t fb = sizeof(float) * (size_t)n;
+
+    StreamIO io;
+    const float *src[8] = {rays->ox, rays->oy, rays->oz, rays->dx, rays->dy, rays->dz, rays->tmin, rays->tmax};
+    const float **dst[8] = {&io.ox, &io.oy, &io.oz, &io.dx, &io.dy, &io.dz, &io.tmin, &io.tmax};
+    for (int k = 0; k < 8; k++) {
+        *dst[k] = nullptr;
+        if (!src[k]) continue;                  // optional tmin / tmax stream: the scalar is used
+        WPT_CUDA(cudaMemcpyAsync(slot(k), src[k], fb, cudaMemcpyHostToDevice, st));
+        *dst[k] = slot(k);
+    }
+    io.tmin_s = rays->tmin_scalar; io.tmax_s = rays->tmax_scalar;
+    io.mask = nullptr; io.mask_size = mask_size;
+    if (mask) {
+        WPT_CUDA(cudaMemcpyAsync(dm, mask, mask_size == 1 ? 1 : n, cudaMemcpyHostToDevice, st));
+        io.mask = dm;
+    }
+    // The area still holds the previous call's results.  The kernel writes t, u, v only where it finds a hit and
+    // nothing at all on masked lanes, and those lanes must come back with the caller's values: upload them first.
+    io.tri_id = reinterpret_cast<int32_t *>(slot(8)); io.t = slot(9); io.u = slot(10); io.v = slot(11);
+    WPT_CUDA(cudaMemcpyAsync(io.tri_id, hits->tri_id, fb, cudaMemcpyHostToDevice, st));
+    WPT_CUDA(cudaMemcpyAsync(io.t, hits->t, fb, cudaMemcpyHostToDevice, st));
+    WPT_CUDA(cudaMemcpyAsync(io.u, hits->u, fb, cudaMemcpyHostToDevice, st));
+    WPT_CUDA(cudaMemcpyAsync(io.v, hits->v, fb, cudaMemcpyHostToDevice, st));
+    WPT_CUDA(cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st));   // the kernel's ray counter has to start at zero
+    launch_trace_streams(s->view, io, n, cursor, s->num_sms, g_default_tune, st);
+    WPT_CUDA(cudaGetLastError());
+    WPT_CUDA(cudaMemcpyAsync(hits->tri_id, io.tri_id, fb, cudaMemcpyDeviceToHost, st));
+    WPT_CUDA(cudaMemcpyAsync(hits->t, io.t, fb, cudaMemcpyDeviceToHost, st));
+    WPT_CUDA(cudaMemcpyAsync(hits->u, io.u, fb, cudaMemcpyDeviceToHost, st));
+    WPT_CUDA(cudaMemcpyAsync(hits->v, io.v, fb, cudaMemcpyDeviceToHost, st));
+    WPT_CUDA(cudaStreamSynchronize(st));
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // ThinlensCamera ctor, src/pinhole.h:9-25
 extern "C" int wpt_camera_init(wpt_camera *c, const float from[3], const float at[3], const float up[3],
                                float lens_radius, float focal_dist, float fov_y, float film_size_y)
