@@ -3,13 +3,14 @@
 // normalise, write wurst.pfm.  Same statement order; the per-sample / per-bounce loop body
 // (main.cpp:385-426) is the one call PathLoop::render.
 //
-//   wurst [scene.obj] [out.pfm] [width height num_samples num_bounces] [--kd] [--gpus N]
+//   wurst [scene.obj [out.pfm [width [height [num_samples [num_bounces]]]]]] [--kd] [--gpus N]     (flags anywhere)
 // --gpus N shards the samples over N GPUs of the box (ShardedPathLoop: one wpt_film_reduce per frame), no Python.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <vector>
 
 #include "wpt_shim.hpp"
 
@@ -17,18 +18,35 @@ using namespace wpt_shim;
 
 int main(int argc, char **argv)
 {
-    // all const (src/main.cpp:357-362)
-    const char *obj = argc > 1 ? argv[1] : "mitsuba.obj";
-    const char *out = argc > 2 ? argv[2] : "wurst.pfm";
-    const int width = argc > 3 ? std::atoi(argv[3]) : 512;
-    const int height = argc > 4 ? std::atoi(argv[4]) : 512;
-    const int num_samples = argc > 5 ? std::atoi(argv[5]) : 100;
-    const int num_bounces = argc > 6 ? std::atoi(argv[6]) : 2;
+    // flags may stand anywhere; what is left are the reference's positional arguments
     bool use_kd = false;
     int n_gpus = 1;
+    std::vector<const char *> pos;
     for (int i = 1; i < argc; i++) {
-        use_kd = use_kd || std::strcmp(argv[i], "--kd") == 0;
-        if (std::strcmp(argv[i], "--gpus") == 0 && i + 1 < argc) n_gpus = std::atoi(argv[i + 1]);
+        if (std::strcmp(argv[i], "--kd") == 0) use_kd = true;
+        else if (std::strcmp(argv[i], "--gpus") == 0) {
+            if (i + 1 >= argc) { std::cerr << "wurst: --gpus needs a count" << std::endl; return 2; }
+            n_gpus = std::atoi(argv[++i]);
+        } else if (std::strncmp(argv[i], "--", 2) == 0) {
+            std::cerr << "usage: wurst [scene.obj [out.pfm [width [height [samples [bounces]]]]]] [--kd] [--gpus N]" << std::endl;
+            return 2;
+        } else pos.push_back(argv[i]);
+    }
+    const size_t np = pos.size();
+    // all const (src/main.cpp:357-362)
+    const char *obj = np > 0 ? pos[0] : "mitsuba.obj";
+    const char *out = np > 1 ? pos[1] : "wurst.pfm";
+    const int width = np > 2 ? std::atoi(pos[2]) : 512;
+    const int height = np > 3 ? std::atoi(pos[3]) : 512;
+    const int num_samples = np > 4 ? std::atoi(pos[4]) : 100;
+    const int num_bounces = np > 5 ? std::atoi(pos[5]) : 2;
+    if (np > 6 || width <= 0 || height <= 0 || num_samples <= 0 || num_bounces <= 0) {
+        std::cerr << "wurst: width, height, samples and bounces must be positive integers (at most six positional arguments)" << std::endl;
+        return 2;
+    }
+    if (n_gpus < 1 || (n_gpus > 1 && n_gpus > wpt_device_count())) {
+        std::cerr << "wurst: --gpus " << n_gpus << ": this box has " << wpt_device_count() << " CUDA device(s)" << std::endl;
+        return 2;
     }
     if (n_gpus > 1) {
         try {

@@ -260,7 +260,10 @@ int  wpt_renderer_set_depth_seeding(wpt_renderer *r, int on);
  * distances are all-gathered on `nccl_comm` (ncclAllGather, W*H floats in total) inside wpt_render, on its stream.
  * EVERY rank of the communicator must then call wpt_render for every frame (it is a collective), with the same camera
  * kind, tmax and depth-seeding setting; the pre-pass then runs whatever the rank's own sample count (no >= 8 rule).  The seeds, hence
- * the frame, are bit-identical to the unsharded pre-pass.  nccl_comm = NULL or n_ranks <= 1 switches it off. */
+ * the frame, are bit-identical to the unsharded pre-pass.  nccl_comm = NULL or n_ranks <= 1 switches it off.
+ * Ranks that disagree on any of those (one with a thin lens, a finite tmax or seeding switched off) do not all enter
+ * the all-gather: the others then wait in it for ever, with no diagnostic — NCCL has no timeout of its own.
+ * WPT_E_INVALID for more ranks than pixels. */
 int  wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, int rank, int n_ranks);
 /* Fused tail: bounces >= first_bounce of every pass run in ONE launch of the traversal kernel with the shading step
  * fused in (a path whose segment ends is shaded by its own lane and continues in place) instead of one trace + one

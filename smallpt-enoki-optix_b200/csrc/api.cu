@@ -4,6 +4,7 @@
 #include <nccl.h>   // types and prototypes only: the library is bound with dlopen (wpt_film_reduce)
 #include <nvtx3/nvToolsExt.h>
 
+#include <fcntl.h>
 #include <unistd.h>
 
 #include <atomic>
@@ -155,13 +156,35 @@ struct TreeFileHeader {
     uint32_t version, n_tris, n_nodes, max_depth;
     uint64_t n_blocks, n_level_nodes, n_level_begin;
     double sah_cost, build_ms;
+    uint64_t layout_tag, payload_hash;
 };
-constexpr uint64_t kTreeMagic = 0x3154504257ull;   // "WBPT1"
+constexpr uint64_t kTreeMagic = 0x3254504257ull;   // "WBPT2"
+// bump when bvh_build.cpp starts to produce different trees or block contents for the same mesh: WPT_VERSION alone
+// does not change with every builder edit, and a file left behind by an older build must not be taken for current
+constexpr uint64_t kBuilderRevision = 3;
+constexpr uint64_t kTreeLayoutTag = (uint64_t)sizeof(Block64) | (uint64_t)kWidth << 8 | (uint64_t)kMaxLeafTris << 16 |
+                                    (uint64_t)kStackSize << 24 | kBuilderRevision << 32;
 uint64_t fnv1a(const void *p, size_t n, uint64_t h)
 {
     const uint8_t *b = static_cast<const uint8_t *>(p);
     for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 0x100000001b3ull; }
     return h;
+}
+// FNV-1a over 64-bit words (n a multiple of 4 bytes; a trailing half word is folded in as is): the payload of a 10 M
+// triangle tree is 0.7 GB, byte-wise hashing would cost more than the disk read
+uint64_t fnv1a_words(const void *p, size_t n, uint64_t h)
+{
+    const uint8_t *b = static_cast<const uint8_t *>(p);
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h ^= w; h *= 0x100000001b3ull; h ^= h >> 29; }
+    return fnv1a(b + i, n - i, h);
+}
+uint64_t tree_payload_hash(const BuiltBvh &b)
+{
+    uint64_t h = 0xcbf29ce484222325ull;
+    h = fnv1a_words(b.blocks.data(), b.blocks.size() * sizeof(Block64), h);
+    h = fnv1a_words(b.level_nodes.data(), b.level_nodes.size() * sizeof(uint32_t), h);
+    return fnv1a_words(b.level_begin.data(), b.level_begin.size() * sizeof(uint32_t), h);
 }
 uint64_t mesh_hash(const wpt_scene *s)
 {
@@ -169,30 +192,79 @@ uint64_t mesh_hash(const wpt_scene *s)
     h = fnv1a(s->pos.data(), s->pos.size() * sizeof(float), h);
     return fnv1a(s->pidx.data(), s->pidx.size() * sizeof(int32_t), h);
 }
+// What the kernels take on trust from a tree: max_depth picks the traversal stack (a fixed shared-memory stack for
+// shallow trees), `base` + child counts are followed without a range check, level_begin drives the refit sweep.  A
+// cache file is outside input, so all of that is checked here and a file that fails any check is ignored (the tree is
+// then built): header consistent, payload checksum, every node's children inside the buffer, every leaf triangle's
+// face index inside the mesh, the level list a partition of the nodes.
+bool tree_consistent(const TreeFileHeader &h, const BuiltBvh &b)
+{
+    if (h.max_depth == 0 || h.max_depth > (uint32_t)kStackSize - 1) return false;
+    if (h.n_level_begin < 2 || h.n_level_begin != (uint64_t)h.max_depth + 1) return false;
+    if (h.n_level_nodes != h.n_nodes || h.n_nodes == 0) return false;
+    if (b.level_begin.front() != 0 || b.level_begin.back() != h.n_level_nodes) return false;
+    for (size_t k = 1; k < b.level_begin.size(); k++)
+        if (b.level_begin[k] < b.level_begin[k - 1]) return false;
+    if (b.level_begin[1] != 1 || b.level_nodes[0] != 0) return false;              // level 0 is the root, block 0
+    uint64_t n_tri_blocks = 0;
+    for (uint32_t idx : b.level_nodes) {
+        if (idx >= h.n_blocks) return false;
+        const Node7 &n = b.blocks[idx].node;
+        const uint32_t imask = n.yhi[7], cnt2 = (uint32_t)n.zlo[7] | ((uint32_t)n.zhi[7] << 8);
+        if (imask & 0x80u) return false;
+        uint32_t n_int = 0, n_leaf = 0;
+        for (int s = 0; s < kWidth; s++) {
+            const uint32_t cnt = (cnt2 >> (2 * s)) & 3u;
+            if ((imask >> s) & 1u) { n_int++; if (cnt) return false; }
+            else n_leaf += cnt;
+        }
+        if (n.base == 0 || (uint64_t)n.base + n_int + n_leaf > h.n_blocks) return false;
+        for (uint32_t k = 0; k < n_leaf; k++) {
+            const int32_t prim = b.blocks[(size_t)n.base + n_int + k].tri.prim;
+            if (prim < 0 || (uint32_t)prim >= h.n_tris) return false;
+        }
+        n_tri_blocks += n_leaf;
+    }
+    return n_tri_blocks + h.n_nodes == h.n_blocks;
+}
 bool tree_load(const char *path, uint64_t hash, uint32_t n_tris, BuiltBvh &b)
 {
     FILE *f = std::fopen(path, "rb");
     if (!f) return false;
     TreeFileHeader h;
-    bool ok = std::fread(&h, sizeof h, 1, f) == 1 && h.magic == kTreeMagic && h.version == WPT_VERSION && h.mesh_hash == hash &&
-              h.n_tris == n_tris && h.n_blocks <= kMaxBlocks && h.n_level_nodes <= h.n_blocks && h.n_level_begin <= 64;
+    bool ok = std::fread(&h, sizeof h, 1, f) == 1 && h.magic == kTreeMagic && h.version == WPT_VERSION &&
+              h.layout_tag == kTreeLayoutTag && h.mesh_hash == hash && h.n_tris == n_tris && h.n_blocks >= 1 &&
+              h.n_blocks <= kMaxBlocks && h.n_level_nodes <= h.n_blocks && h.n_level_begin <= 64;
+    if (ok) {
+        // the sizes must be those of the file before anything is allocated for them
+        const long at = std::ftell(f);
+        ok = at >= 0 && std::fseek(f, 0, SEEK_END) == 0;
+        const long end = ok ? std::ftell(f) : -1;
+        ok = ok && end >= 0 && (uint64_t)(end - at) == h.n_blocks * sizeof(Block64) + (h.n_level_nodes + h.n_level_begin) * sizeof(uint32_t) &&
+             std::fseek(f, at, SEEK_SET) == 0;
+    }
     if (ok) {
         b.blocks.resize(h.n_blocks); b.level_nodes.resize(h.n_level_nodes); b.level_begin.resize(h.n_level_begin);
         ok = std::fread(b.blocks.data(), sizeof(Block64), h.n_blocks, f) == h.n_blocks &&
              std::fread(b.level_nodes.data(), sizeof(uint32_t), h.n_level_nodes, f) == h.n_level_nodes &&
              std::fread(b.level_begin.data(), sizeof(uint32_t), h.n_level_begin, f) == h.n_level_begin;
+        ok = ok && tree_payload_hash(b) == h.payload_hash && tree_consistent(h, b);
         b.n_nodes = h.n_nodes; b.n_tris = h.n_tris; b.max_depth = h.max_depth; b.sah_cost = h.sah_cost; b.build_ms = h.build_ms;
     }
     std::fclose(f);
+    if (!ok) b = BuiltBvh();
     return ok;
 }
 void tree_store(const char *path, uint64_t hash, const BuiltBvh &b)
 {
     const std::string tmp = std::string(path) + ".tmp" + std::to_string((unsigned long long)hash & 0xffff) + std::to_string((long)getpid());
-    FILE *f = std::fopen(tmp.c_str(), "wb");
-    if (!f) return;                                   // a cache that cannot be written is not an error
+    // 0600, and never through a file someone else put there (O_EXCL): caches tend to live in shared directories
+    ::unlink(tmp.c_str());                            // left by a run of the same pid that died half-way
+    const int fd = ::open(tmp.c_str(), O_WRONLY | O_CREAT | O_EXCL | O_NOFOLLOW, 0600);
+    FILE *f = fd >= 0 ? ::fdopen(fd, "wb") : nullptr;
+    if (!f) { if (fd >= 0) ::close(fd); return; }     // a cache that cannot be written is not an error
     TreeFileHeader h{kTreeMagic, hash, WPT_VERSION, b.n_tris, b.n_nodes, b.max_depth, b.blocks.size(), b.level_nodes.size(),
-                     b.level_begin.size(), b.sah_cost, b.build_ms};
+                     b.level_begin.size(), b.sah_cost, b.build_ms, kTreeLayoutTag, tree_payload_hash(b)};
     const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(b.blocks.data(), sizeof(Block64), b.blocks.size(), f) == b.blocks.size() &&
                     std::fwrite(b.level_nodes.data(), sizeof(uint32_t), b.level_nodes.size(), f) == b.level_nodes.size() &&
                     std::fwrite(b.level_begin.data(), sizeof(uint32_t), b.level_begin.size(), f) == b.level_begin.size();
@@ -212,7 +284,10 @@ static int scene_commit(wpt_scene *s, int device, int builder, const char *cache
     if (s->committed) {
         if (s->pos_on_device_newer && s->d_pos) {
             // the vertices were last moved by wpt_scene_refit_device: rebuild from those, not from the stale host copy
+            // the refit and its copy into d_pos were queued on the caller's stream; a non-blocking stream (every PyTorch
+            // side stream is one) is not ordered against the copy below, so wait for the whole device first
             WPT_CUDA(cudaSetDevice(s->device));
+            WPT_CUDA(cudaDeviceSynchronize());
             WPT_CUDA(cudaMemcpy(s->pos.data(), s->d_pos, s->pos.size() * sizeof(float), cudaMemcpyDeviceToHost));
             for (float x : s->pos)
                 if (!std::isfinite(x)) return fail(WPT_E_INVALID, "wpt_scene_commit: non-finite vertex in the device-side positions");
@@ -900,6 +975,7 @@ extern "C" int wpt_renderer_set_depth_shard(wpt_renderer *r, void *nccl_comm, in
     if (r->in_flight && !r->captured) return fail(WPT_E_STATE, "wpt_renderer_set_depth_shard: render in flight");
     if (!nccl_comm || n_ranks <= 1) { r->shard_comm = nullptr; r->shard_rank = 0; r->shard_n = 1; return WPT_OK; }
     if (rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_renderer_set_depth_shard: bad rank");
+    if ((uint64_t)n_ranks > (uint64_t)r->W * r->H) return fail(WPT_E_INVALID, "wpt_renderer_set_depth_shard: more ranks than pixels");
     if (int rc = nccl_load()) return rc;
     const uint64_t N = (uint64_t)r->W * r->H, chunk = (N + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
     if (!r->tlane || r->tlane_floats < chunk * (uint64_t)n_ranks) {
@@ -1026,15 +1102,18 @@ extern "C" int wpt_render(wpt_renderer *r, const wpt_camera *cam, const wpt_rend
         const uint32_t lanes = shard ? std::min(N - lane0, chunk) : N;
         WPT_CUDA(cudaMemsetAsync(r->counters, 0, sizeof(PassCounters), st));
         WPT_CUDA(mark(0));
-        launch_raygen(*cam, r->W, r->H, 0, 1, cfg->seed, r->q[0], &r->counters->qcount[0], st, nullptr, 1, lane0, std::max(lanes, 1u));
+        // a trailing rank of an uneven split may own no pixel at all (10 pixels over 8 ranks: chunk 2, ranks 5..7
+        // empty): it launches nothing but still takes part in the all-gather
+        if (lanes) launch_raygen(*cam, r->W, r->H, 0, 1, cfg->seed, r->q[0], &r->counters->qcount[0], st, nullptr, 1, lane0, lanes);
         WPT_CUDA(done());
         WPT_CUDA(mark(1));
-        launch_trace_queue(s->view, r->q[0], r->hits, &r->counters->qcount[0], &r->counters->cursor[0], nullptr,
-                           cfg->tmin, cfg->tmax, std::max(lanes, 1u), s->num_sms, tune, st);
+        if (lanes)
+            launch_trace_queue(s->view, r->q[0], r->hits, &r->counters->qcount[0], &r->counters->cursor[0], nullptr,
+                               cfg->tmin, cfg->tmax, lanes, s->num_sms, tune, st);
         WPT_CUDA(done());
         WPT_CUDA(mark(0));
         if (shard) {
-            launch_depth_pack(r->hits, lanes, r->tlane + (size_t)r->shard_rank * chunk, st);
+            if (lanes) launch_depth_pack(r->hits, lanes, r->tlane + (size_t)r->shard_rank * chunk, st);
             WPT_NCCL(g_nccl.AllGather(r->tlane + (size_t)r->shard_rank * chunk, r->tlane, chunk, ncclFloat32,
                                       reinterpret_cast<ncclComm_t>(r->shard_comm), st));
             launch_depth_seeds_from_lanes(r->tlane, r->W, r->H, r->seed_margin, r->depth, r->seed, st);

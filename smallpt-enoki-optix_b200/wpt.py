@@ -181,24 +181,31 @@ def load_meshes(path, use_kd=False):
     return out
 
 
-class PinnedArray:
-    """float32 numpy array over pinned host memory from wpt_host_alloc (freed with the object)"""
+class _PinnedBlock:
+    """One wpt_host_alloc allocation, exposed to numpy through the array interface: every array made from it — and every
+    view of those — keeps this object as its base, so the memory is returned (wpt_host_free) only after the last of them
+    has gone, never under a live view."""
 
-    def __init__(self, shape):
-        n = int(np.prod(shape))
+    def __init__(self, n_floats):
         self._p = C.c_void_p()
-        _check(lib().wpt_host_alloc(C.c_size_t(4 * n), C.byref(self._p)))
-        buf = (C.c_float * n).from_address(self._p.value)
-        self.array = np.frombuffer(buf, dtype=np.float32).reshape(shape)
+        _check(lib().wpt_host_alloc(C.c_size_t(4 * max(n_floats, 1)), C.byref(self._p)))
+        self.__array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (self._p.value, False), "version": 3}
 
     def __del__(self):
         try:
             if self._p:
-                self.array = None
                 lib().wpt_host_free(self._p)
                 self._p = C.c_void_p()
         except Exception:
             pass
+
+
+class PinnedArray:
+    """float32 numpy array over pinned host memory from wpt_host_alloc.  The allocation belongs to `array` (and to any
+    view taken from it), not to this object: it is freed when the last of them is dropped."""
+
+    def __init__(self, shape):
+        self.array = np.asarray(_PinnedBlock(int(np.prod(shape)))).reshape(shape)
 
 
 def scene_from_obj(path, device=0, use_kd=False):
@@ -455,8 +462,12 @@ class Renderer:
         _check(lib().wpt_render_finish(self._h, C.byref(st), _stream_handle(stream)))
         return _stats_dict(st)
 
-    def render_host(self, camera, spp_begin, spp_count, depth, seed=0, tmin=1e-3, tmax=1e20, out=None):
-        """whole frame to HOST planar film [3, H*W], normalised by spp_count (src/main.cpp:369-439)."""
+    def render_host(self, camera, spp_begin, spp_count, depth, seed=0, tmin=1e-3, tmax=1e20, out=None, copy=True):
+        """whole frame to HOST planar film [3, H*W], normalised by spp_count (src/main.cpp:369-439).  Without `out` the
+        frame lands in the renderer's own pinned film; by default the caller gets a copy of it (an array of its own, at
+        the price of one more pass over 12 bytes per pixel on the host).  copy=False hands out the pinned film itself: no
+        extra pass, but the NEXT render_host of this renderer overwrites it.  With `out` the frame is written there and
+        `out` is returned."""
         N = self.width * self.height
         if out is None:
             # the renderer's own pinned film (wpt_host_alloc): the D2H copies are plain DMA transfers
@@ -468,7 +479,8 @@ class Renderer:
         st = Stats()
         _check(lib().wpt_render_host(self._h, C.byref(camera.c), C.byref(cfg), C.c_void_p(film[0].ctypes.data),
                                      C.c_void_p(film[1].ctypes.data), C.c_void_p(film[2].ctypes.data), C.byref(st)))
-        return (film if film is not getattr(getattr(self, "_pinned", None), "array", None) else film.copy()), _stats_dict(st)
+        own = film is getattr(getattr(self, "_pinned", None), "array", None)
+        return (film.copy() if own and copy else film), _stats_dict(st)
 
     def close(self):
         if self._h:

@@ -32,7 +32,10 @@ def _worker(rank, world, port, q):
     out = []
     # (sharded pre-pass?, samples): 15 samples split 8 / 7 — the ranks disagree on the ">= 8 samples" rule of the
     # unsharded pre-pass, the sharded one must still be entered by both (it is a collective)
-    for shard, spp in ((0, 24), (1, 24), (1, 15)):
+    # with three or more ranks also a 3 x 2 image: ceil(6 / 4) = 2 pixels per rank leaves the last rank of four without
+    # a single pixel of the pre-pass — it must launch nothing and still join the all-gather
+    cases = [(0, 24, W, H), (1, 24, W, H), (1, 15, W, H)] + ([(1, 16, 3, 2)] if world >= 3 else [])
+    for shard, spp, W, H in cases:
         r = wpt.Renderer(scene, W, H, 8)
         if shard:
             r.set_depth_shard(red.comm, rank, world)
@@ -43,11 +46,11 @@ def _worker(rank, world, port, q):
         st = r.finish()
         segs = torch.tensor([st["segments"], st["retraced"]], dtype=torch.int64)
         dist.reduce(segs, dst=0)
-        out.append((film, segs, spp))
+        out.append((film, segs, spp, W, H))
         r.close()
     if rank == 0:
         ok = []
-        for f, s, spp in out:
+        for f, s, spp, W, H in out:
             r = wpt.Renderer(scene, W, H, 8)
             whole = torch.zeros(3, W * H, device="cuda")
             r.render(cam, whole, 0, spp, depth, seed=9)
@@ -59,19 +62,27 @@ def _worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_two_rank_sharded_frame_equals_one_gpu():
+def _run(world):
     import torch
     import torch.multiprocessing as mp
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs (run under gpurun --gpus 2)")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (run under gpurun --gpus %d)" % (world, world))
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29600 + (os.getpid() % 2000)
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    port = 29600 + (os.getpid() % 2000) + world
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = q.get(timeout=300)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    assert res == ([True, True, True], True, True)
+    return res
+
+
+def test_two_rank_sharded_frame_equals_one_gpu():
+    assert _run(2) == ([True, True, True], True, True)
+
+
+def test_four_rank_sharded_frame_with_a_rank_that_owns_no_pixel():
+    assert _run(4) == ([True, True, True, True], True, True)

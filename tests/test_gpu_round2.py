@@ -414,3 +414,125 @@ def test_commit_cached_shares_one_host_build(tmp_path):
     path.write_bytes(bytes(raw))                                # damaged header
     e = wpt.scene_from(other, cache_path=path)
     assert e.from_cache is False and wpt.scene_from(other, cache_path=path).from_cache is True
+
+
+def _tree_words_hash(chunks):
+    """csrc/api.cu tree_payload_hash: FNV-1a over 64-bit words with an extra xor-shift, the trailing half word bytewise"""
+    M = (1 << 64) - 1
+    h = 0xcbf29ce484222325
+    for raw in chunks:
+        k = len(raw) // 8 * 8
+        for w in np.frombuffer(raw[:k], "<u8").tolist():
+            h ^= w
+            h = (h * 0x100000001b3) & M
+            h ^= h >> 29
+        for byte in raw[k:]:
+            h ^= byte
+            h = (h * 0x100000001b3) & M
+    return h
+
+
+def test_commit_cached_checks_what_it_loads(tmp_path):
+    """a tree file is outside input.  max_depth picks the traversal stack and `base` is followed without a
+    range check by the kernels, so a stale, damaged or forged file must be refused at load (and the tree built), even
+    when its checksum has been made to fit."""
+    import struct
+    import torch
+    import wpt
+    sd = scenes.knob(40, 16)
+    path = tmp_path / "tree.bin"
+    ref = wpt.scene_from(sd, cache_path=path)
+    good = path.read_bytes()
+    assert wpt.scene_from(sd, cache_path=path).from_cache is True
+    assert (path.stat().st_mode & 0o077) == 0                    # written 0600
+    HDR = 88                                                     # TreeFileHeader
+    (magic, mhash, version, n_tris, n_nodes, max_depth, n_blocks, n_lnodes, n_lbegin, sah, bms, tag,
+     phash) = struct.unpack("<QQIIIIQQQddQQ", good[:HDR])
+    assert n_lbegin == max_depth + 1 and n_lnodes == n_nodes and len(good) == HDR + 64 * n_blocks + 4 * (n_lnodes + n_lbegin)
+    blocks = good[HDR:HDR + 64 * n_blocks]
+    lnodes = good[HDR + 64 * n_blocks:HDR + 64 * n_blocks + 4 * n_lnodes]
+    lbegin = good[HDR + 64 * n_blocks + 4 * n_lnodes:]
+    assert _tree_words_hash([blocks, lnodes, lbegin]) == phash   # this test's restatement of the checksum is right
+
+    def header(**kw):
+        f = dict(magic=magic, mhash=mhash, version=version, n_tris=n_tris, n_nodes=n_nodes, max_depth=max_depth,
+                 n_blocks=n_blocks, n_lnodes=n_lnodes, n_lbegin=n_lbegin, sah=sah, bms=bms, tag=tag, phash=phash)
+        f.update(kw)
+        return struct.pack("<QQIIIIQQQddQQ", *f.values())
+
+    o, d = util.random_rays(sd, 20_000, seed=8)
+    ot, dt = _streams(torch, o, d)
+    want = ref.intersect(ot, dt)
+
+    def refused(raw, what):
+        path.write_bytes(raw)
+        s = wpt.scene_from(sd, cache_path=path)
+        assert s.from_cache is False, what
+        assert s.stats()["max_depth"] == max_depth, what
+        for x, y in zip(want, s.intersect(ot, dt)):
+            assert torch.equal(torch.nan_to_num(x), torch.nan_to_num(y)), what
+        now = path.read_bytes()                                  # and the file has been replaced by a sound one
+        assert now[:64] == good[:64] and now[72:] == good[72:], what     # (bytes 64..72: the build time)
+
+    refused(header(max_depth=40) + good[HDR:], "stack depth beyond the traversal stack")
+    refused(header(max_depth=max_depth - 1) + good[HDR:], "depth that disagrees with the level table")
+    refused(header(tag=tag ^ (1 << 32)) + good[HDR:], "another builder revision")
+    refused(good[:-4], "truncated")
+    refused(good + b"\0" * 64, "trailing bytes")
+    flipped = bytearray(good); flipped[HDR + 64 * (n_blocks // 2) + 17] ^= 0x40
+    refused(bytes(flipped), "payload changed, checksum not")
+    # forged with a fitting checksum: the root's `base` points past the buffer
+    forged = bytearray(blocks); forged[12:16] = struct.pack("<I", n_blocks)
+    refused(header(phash=_tree_words_hash([bytes(forged), lnodes, lbegin])) + bytes(forged) + lnodes + lbegin,
+            "child run outside the buffer")
+    # ... a leaf triangle whose face index is outside the mesh (last block of a breadth-first tree is a triangle)
+    forged = bytearray(blocks); forged[64 * (n_blocks - 1) + 48:64 * (n_blocks - 1) + 52] = struct.pack("<i", n_tris)
+    refused(header(phash=_tree_words_hash([bytes(forged), lnodes, lbegin])) + bytes(forged) + lnodes + lbegin,
+            "face index outside the mesh")
+    # ... a level table that does not end at the node count
+    lb = np.frombuffer(lbegin, "<u4").copy(); lb[-1] += 1
+    refused(header(phash=_tree_words_hash([blocks, lnodes, lb.tobytes()])) + blocks + lnodes + lb.tobytes(),
+            "level table does not end at the node count")
+
+
+def test_depth_shard_refuses_more_ranks_than_pixels():
+    """a rank count beyond W*H would leave ranks whose pre-pass slice starts outside the image"""
+    import ctypes as C
+    import wpt
+    sd = scenes.cornell(4)
+    r = wpt.Renderer(wpt.scene_from(sd), 3, 2, 1)
+    rc = wpt.lib().wpt_renderer_set_depth_shard(r._h, C.c_void_p(1), C.c_int(0), C.c_int(7))
+    assert rc == 1 and b"more ranks than pixels" in wpt.lib().wpt_last_error()
+    assert wpt.lib().wpt_renderer_set_depth_shard(r._h, None, C.c_int(0), C.c_int(7)) == 0      # NULL comm: switched off
+    r.close()
+
+
+def test_pinned_film_outlives_the_objects_that_made_it():
+    """arrays over wpt_host_alloc memory own it — dropping the PinnedArray or the Renderer does not free the
+    film under a live view; render_host(copy=False) hands out the pinned film itself, the default a private copy."""
+    import gc
+    import wpt
+    sd = scenes.cornell(8)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    pin = wpt.PinnedArray((3, 1000))
+    row = pin.array[1]
+    row[:] = 7.0
+    del pin
+    gc.collect()
+    junk = [wpt.PinnedArray((3, 1000)) for _ in range(8)]       # would reuse the block had it been freed
+    for j in junk:
+        j.array[:] = -1.0
+    assert (row == 7.0).all()
+    r = wpt.Renderer(scene, 32, 32, 2)
+    a, _ = r.render_host(cam, 0, 4, 4, seed=3)
+    live, _ = r.render_host(cam, 0, 4, 4, seed=3, copy=False)
+    assert np.array_equal(a, live) and not np.shares_memory(a, live)
+    again, _ = r.render_host(cam, 4, 4, 4, seed=3, copy=False)
+    assert np.shares_memory(again, live) and not np.array_equal(a, live)      # the next frame overwrote the live film
+    keep = live[0]
+    want = keep.copy()
+    r.close()
+    del r, live, again
+    gc.collect()
+    assert np.array_equal(keep, want)

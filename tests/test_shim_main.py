@@ -42,6 +42,33 @@ def test_main_fails_loudly_without_a_device(tmp_path):
     assert r.returncode == 1 and "no CUDA device" in r.stderr and not (tmp_path / "o.pfm").exists()
 
 
+def test_main_checks_its_command_line(tmp_path):
+    """flags may stand anywhere and are not read as positional values; sizes and the GPU count are checked
+    before anything is loaded (exit code 2, nothing written)."""
+    out = tmp_path / "o.pfm"
+    for argv, needle in (([OBJ, str(out), "--gpus"], "needs a count"),
+                         ([OBJ, str(out), "0", "16", "1", "2"], "positive"),
+                         ([OBJ, str(out), "16", "16", "1", "2", "7"], "positional"),
+                         ([OBJ, str(out), "--frobnicate"], "usage"),
+                         ([OBJ, str(out), "--gpus", "4096", "16", "16", "1", "2"], "CUDA device"),
+                         ([OBJ, str(out), "--gpus", "0"], "CUDA device")):
+        r = subprocess.run([WURST] + argv, capture_output=True, text=True)
+        assert r.returncode == 2 and needle in r.stderr, (argv, r.returncode, r.stderr)
+    assert not out.exists()
+
+
+@pytest.mark.gpu
+def test_main_takes_flags_before_the_positionals(tmp_path):
+    """`wurst scene.obj out.pfm --gpus 1 --kd 32 24 4 2` used to read width = atoi("--gpus")"""
+    a, b = tmp_path / "a.pfm", tmp_path / "b.pfm"
+    for out, argv in ((a, [OBJ, str(a), "32", "24", "4", "2", "--kd", "--gpus", "1"]),
+                      (b, ["--kd", OBJ, str(b), "--gpus", "1", "32", "24", "4", "2"])):
+        r = subprocess.run([WURST] + argv, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    ia, ib = _read_pfm(a), _read_pfm(b)
+    assert ia.shape == ib.shape == (3, 32 * 24) and np.allclose(ia, ib, rtol=0, atol=2e-6)
+
+
 @pytest.mark.gpu
 def test_main_writes_the_same_image_as_the_python_mirror(tmp_path):
     import wpt
