@@ -20,8 +20,10 @@ import argparse
 import ctypes as C
 import json
 import os
+import shutil
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -166,15 +168,28 @@ def cpu_reference_run(sd, W, H, depth, spp, budget_s, threads=0):
     return seg / dt / 1e6, seg, dt, kind, cores
 
 
+def frame_config(args, sd, W, H, spp_total, depth):
+    """what is rendered — the same dict, key for key and value for value, in both arms (the driver compares them); how an
+    arm renders it is that arm's `engine` object"""
+    return {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H, "spp": spp_total,
+            "depth": depth, "camera": "pinhole, the workload's default view", "albedo": "all materials white" if bool((sd.albedo == 1).all()) else "per-material greys",
+            "l2": "GPU arm: no flush, the inputs of a step exceed the 126 MB L2 — ray/hit queues of a default pass %.0f MB "
+                  "(96 B per path in flight) + the BVH; CPU arm: the same paths, host caches" % (
+                      W * H * max(1, min(spp_total, 64, (1 << 28) // (W * H))) * 96 / 1e6)}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     import scenes
     gen, W, H, spp, depth = workload(args.workload)
+    if args.spp:
+        spp = args.spp
     sd = gen()
-    # bounded sample: the full frame at 16 spp per step (C3: ~85 M segments, ~2 s on 16 cores)
-    sample_spp = min(16, spp)
+    # one step = the whole frame, all `spp` samples, like a step of the GPU arm (C3: 340 M segments, ~6 s on 16 cores,
+    # ~3 s on 32: 25 steps stay within a few minutes).  --ref-spp bounds it for slower hosts.
+    sample_spp = min(args.ref_spp, spp) if args.ref_spp > 0 else spp
     times, segs = [], 0
     kind, cores = "port", 1
     for i in range(args.warmup + args.steps):
@@ -187,10 +202,14 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
-                       "spp": spp, "depth": depth, "spp_per_step": sample_spp, "sample": sample,
+            "config": frame_config(args, sd, W, H, spp, depth),
+            "engine": {"spp_per_step": sample_spp, "sample": sample, "threads": cores,
                        "timing": "host steady clock around the render (a CPU arm has no device clock); BVH build outside"},
-            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+            "ms_per_frame": 1e3 * tot / len(times) * spp / sample_spp, "segments_per_step": segs / len(times),
+            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample,
+                             "mrays_per_core": val / cores,
+                             "note": "the GPU/CPU ratio is a property of this box's host CPU (16 cores on one pool box, "
+                                     "32 on another): compare Mrays/s per core across boxes"},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -238,7 +257,11 @@ def run_ours(args):
     # (wpt_scene_commit_cached); untimed, like the reference's own build (src/main.cpp:366 precedes :373)
     cache = None
     if world > 1:
-        cache = "/dev/shm/wpt_tree_%s_%s.bin" % (args.workload, os.environ.get("MASTER_PORT", "0"))
+        # a directory of this run's own (0700, random name), announced by rank 0: nothing a crashed or foreign run left
+        # in /dev/shm can be picked up, and the library checks what it loads anyway (csrc/api.cu tree_load)
+        box = [tempfile.mkdtemp(prefix="wpt_tree_", dir="/dev/shm") if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        cache = os.path.join(box[0], "%s.bin" % args.workload)
         if rank != 0:
             dist.barrier()
     scene = wpt.scene_from(sd, device=local, cache_path=cache)
@@ -332,7 +355,7 @@ def run_ours(args):
     # render -> (N>1: reduce onto rank 0) -> 1/spp -> D2H of the planar film into PINNED host memory
     pinned = wpt.PinnedArray((3, N))
     host_film = pinned.array
-    e_steps = max(1, min(args.steps, 5))
+    e_steps = max(1, args.steps)           # the same number of frames as the device-timed loop
 
     def e2e_step():
         if world == 1:
@@ -370,6 +393,29 @@ def run_ours(args):
                     "into pinned host memory" if world == 1 else
                     "per rank: film zero + this rank's samples; wpt_film_reduce onto rank 0; rank 0: 1/spp + D2H of the "
                     "reduced film into pinned host memory; host clock, max over ranks")}
+
+    # ---- sameness across N: the UN-normalised frame, reduced onto rank 0, summed per channel on the host in fp64.
+    # Every contribution of an all-white scene is exactly 1.0 and a pixel holds at most spp of them, so the film is
+    # integers and its sums are exact: they — and the segment count — must be the same numbers at N = 1, 2, 4, 8
+    # (src/main.cpp:407,429 is the sum that is sharded).  One untimed frame.
+    film.zero_()
+    r.render(cam, film, spp_begin, spp, depth, seed=SEED)
+    if reducer is not None:
+        reducer.reduce(film, 0)
+    cst = r.finish()
+    cseg = torch.tensor([cst["segments"]], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(cseg, op=dist.ReduceOp.SUM)
+    checksum = None
+    if rank == 0:
+        hf = film.cpu().numpy().astype(np.float64)
+        sums = hf.sum(axis=1)
+        checksum = {"film_checksum": [int(round(x)) for x in sums],
+                    "exact": bool(np.all(hf == np.rint(hf))),
+                    "escaped_paths": int(round(sums[0])) if np.all(hf[0] == np.rint(hf[0])) else None,
+                    "segments": int(cseg.item()),
+                    "what": "per-channel sums of the un-normalised reduced film (fp64 on the host) of one untimed frame; "
+                            "`exact`: every pixel an integer (all-white scene), so the sums are too"}
 
     # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
     roof = None
@@ -425,15 +471,15 @@ def run_ours(args):
         mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, 1, 0)      # calibrate
         k = int(max(1, min(spp, round(12.0 / max(dt, 1e-3)))))                       # ~12 s of CPU work
         mr, seg, dt, kind, cores = cpu_reference_run(sd, W, H, depth, k, 0)
-        cpu = {"value": mr, "unit": "Mrays/s", "cores": cores, "kind": kind,
+        cpu = {"value": mr, "unit": "Mrays/s", "cores": cores, "kind": kind, "mrays_per_core": mr / cores,
                "sample": f"same scene/camera, {W}x{H}, depth {depth}, {k} spp of {spp} ({seg} segments, {dt:.1f} s)"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"{args.workload}:{sd.name}", "tris": sd.n_tris, "width": W, "height": H,
-                           "spp": spp, "spp_total": spp_total, "depth": depth, "spp_per_pass": args.spp_per_pass,
+                "config": frame_config(args, sd, W, H, spp_total, depth),
+                "engine": {"spp_this_rank": spp, "spp_per_pass": args.spp_per_pass,
                            "parallelism": f"spp-shard x{world}", "reduce": "wpt_film_reduce (ncclReduce, own communicator)" if world > 1 else None,
                            "overlap_lanes": int(args.overlap), "cuda_graph": bool(args.graph), "depth_seeding": int(args.seeding),
                            "fused_tail_from": st["tail_from"], "trace_variant": args.variant,
@@ -442,14 +488,15 @@ def run_ours(args):
                                N * args.spp_per_pass * 96 / 1e6, (bst["node_bytes"] + bst["tri_bytes"]) / 1e6),
                            "bvh": {"nodes": bst["n_nodes"], "depth": bst["max_depth"], "sah": bst["sah_cost"],
                                    "build_ms": bst["build_ms"], "upload_ms": bst["upload_ms"]}},
+                "film_checksum": checksum["film_checksum"], "checksum": checksum,
                 "ms_per_frame": ms / args.steps, "segments_per_step": segs_all / args.steps,
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "commit_s": commit_s, "tree_shared_through_cache": bool(cache)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
-        if rank == 0 and cache and os.path.exists(cache):
-            os.remove(cache)
+        if rank == 0 and cache:
+            shutil.rmtree(os.path.dirname(cache), ignore_errors=True)
         reducer.close()
         dist.destroy_process_group()
     return 0
@@ -474,6 +521,7 @@ def main():
     ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
     ap.add_argument("--seeding", type=int, default=1, help="1 = depth seeding of the camera rays (default), 0 = off")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--ref-spp", type=int, default=0, help="--impl reference: samples per step (0 = the workload's, like the GPU arm)")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours" and not args.quick:
