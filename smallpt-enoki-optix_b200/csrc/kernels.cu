@@ -49,28 +49,32 @@ __device__ __forceinline__ void lane_to_pixel(uint32_t p, int W, int H, int &x, 
 // shade kernels of bounce 0 are told (QueueIO::seeded, shade_kernel's seeded0).  centre != 0: one ray per pixel
 // through the pixel centre and the lens centre (the depth pre-pass; not a sample of the estimator).
 __global__ void __launch_bounds__(256)
-raygen_kernel(const wpt_camera cam, int W, int H, int spp_first, int spp_in_pass, uint32_t k0, uint32_t k1,
+raygen_kernel(const wpt_camera cam, const CameraFrame cf, int W, int H, int spp_first, int spp_in_pass, uint32_t k0, uint32_t k1,
               RayQueue q, uint32_t *__restrict__ qcount0, const float *__restrict__ seed, int centre,
               uint32_t lane_first, uint32_t lane_count)
 {
-    // lanes [lane_first, lane_first + lane_count) of every sample: the whole frame, or one rank's share of the depth pre-pass
+    // lanes [lane_first, lane_first + lane_count) of every sample: the whole frame, or one rank's share of the depth pre-pass.
+    // A thread owns a lane and walks its samples: the pixel decode and the seed load are paid once per lane, and the
+    // warp's stores of one sample are three coalesced runs at sample * N + lane, as before.
     const uint32_t N = lane_count;
-    const uint32_t total = N * (uint32_t)spp_in_pass;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *qcount0 = total;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t s_local = i / N, p = lane_first + (i - s_local * N);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *qcount0 = N * (uint32_t)spp_in_pass;
+    for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < N; l += gridDim.x * blockDim.x) {
         int x, y;
-        lane_to_pixel(p, W, H, x, y);
+        lane_to_pixel(lane_first + l, W, H, x, y);
         const uint32_t pixel = (uint32_t)y * (uint32_t)W + (uint32_t)x;   // src/main.cpp:379-381
-        uint32_t rnd[4];
-        philox4x32_10(pixel, (uint32_t)spp_first + s_local, 0u, 0u, k0, k1, rnd);
-        float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
-        if (centre) xi[0] = xi[1] = xi[2] = xi[3] = 0.5f;
-        V3 o, d;
-        camera_ray(cam, x, y, W, H, xi, o, d);
-        __stcs(q.a + i, make_float4(o.x, o.y, o.z, __uint_as_float(pixel | (s_local << 24))));
-        __stcs(q.b + i, make_float4(d.x, d.y, d.z, seed ? __ldg(seed + pixel) : 1.0f));   // contrib = 1 (src/main.cpp:391)
-        __stcs(q.c + i, make_float2(1.0f, 1.0f));
+        const float bw = seed ? __ldg(seed + pixel) : 1.0f;                // contrib = 1 (src/main.cpp:391)
+        for (uint32_t s_local = 0; s_local < (uint32_t)spp_in_pass; s_local++) {
+            uint32_t rnd[4];
+            philox4x32_10(pixel, (uint32_t)spp_first + s_local, 0u, 0u, k0, k1, rnd);
+            float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
+            if (centre) xi[0] = xi[1] = xi[2] = xi[3] = 0.5f;
+            V3 o, d;
+            camera_ray(cam, cf, x, y, W, H, xi, o, d);
+            const uint32_t i = s_local * N + l;
+            __stcs(q.a + i, make_float4(o.x, o.y, o.z, __uint_as_float(pixel | (s_local << 24))));
+            __stcs(q.b + i, make_float4(d.x, d.y, d.z, bw));
+            __stcs(q.c + i, make_float2(1.0f, 1.0f));
+        }
     }
 }
 
@@ -79,12 +83,12 @@ void launch_raygen(const wpt_camera &cam, int W, int H, int spp_first, int spp_i
                    uint32_t lane_first, uint32_t lane_count)
 {
     if (lane_count == 0) { lane_first = 0; lane_count = (uint32_t)W * (uint32_t)H; }
-    const uint64_t total = (uint64_t)lane_count * spp_in_pass;
     const uint64_t cap = (uint64_t)device_sms() * 16u;
-    const uint32_t blocks = (uint32_t)((total + 255) / 256 < cap ? (total + 255) / 256 : cap);
-    raygen_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_first, spp_in_pass, (uint32_t)seed,
-                                                       (uint32_t)(seed >> 32), q, qcount0, tmax_seed, centre, lane_first,
-                                                       lane_count);
+    const uint64_t want = ((uint64_t)lane_count + 255) / 256;
+    const uint32_t blocks = (uint32_t)(want < cap ? want : cap);
+    raygen_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, camera_frame_constants(cam, W, H), W, H, spp_first, spp_in_pass,
+                                                       (uint32_t)seed, (uint32_t)(seed >> 32), q, qcount0, tmax_seed, centre,
+                                                       lane_first, lane_count);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -161,7 +165,7 @@ void launch_depth_seeds(const float4 *qa, const int4 *hits, int W, int H, float 
 }
 
 __global__ void __launch_bounds__(256)
-raygen_streams_kernel(const wpt_camera cam, int W, int H, int spp, uint32_t k0, uint32_t k1, float *ox,
+raygen_streams_kernel(const wpt_camera cam, const CameraFrame cf, int W, int H, int spp, uint32_t k0, uint32_t k1, float *ox,
                       float *oy, float *oz, float *dx, float *dy, float *dz)
 {
     const uint32_t N = (uint32_t)W * (uint32_t)H;
@@ -171,7 +175,7 @@ raygen_streams_kernel(const wpt_camera cam, int W, int H, int spp, uint32_t k0, 
         philox4x32_10(pixel, (uint32_t)spp, 0u, 0u, k0, k1, rnd);
         const float xi[4] = { u32_to_unit(rnd[0]), u32_to_unit(rnd[1]), u32_to_unit(rnd[2]), u32_to_unit(rnd[3]) };
         V3 o, d;
-        camera_ray(cam, x, y, W, H, xi, o, d);
+        camera_ray(cam, cf, x, y, W, H, xi, o, d);
         ox[pixel] = o.x; oy[pixel] = o.y; oz[pixel] = o.z;
         dx[pixel] = d.x; dy[pixel] = d.y; dz[pixel] = d.z;
     }
@@ -182,7 +186,7 @@ void launch_raygen_streams(const wpt_camera &cam, int W, int H, int spp_index, u
 {
     const uint32_t N = (uint32_t)W * H;
     const uint32_t blocks = (N + 255) / 256;
-    raygen_streams_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, W, H, spp_index, (uint32_t)seed,
+    raygen_streams_kernel<<<blocks ? blocks : 1, 256, 0, st>>>(cam, camera_frame_constants(cam, W, H), W, H, spp_index, (uint32_t)seed,
                                                                (uint32_t)(seed >> 32), ox, oy, oz, dx, dy, dz);
 }
 

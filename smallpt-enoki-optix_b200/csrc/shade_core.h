@@ -104,7 +104,20 @@ WPT_HD V3 frame_to_world(V3 n, V3 l)
 }
 
 // ---------------------------------------------------------------- camera (src/pinhole.h:27-56)
-WPT_HD void camera_ray(const wpt_camera &c, int px, int py, int W, int H, const float xi[4], V3 &org, V3 &dir)
+// The two quantities of sample_dir that depend on the camera and the resolution only (pinhole.h:41-47): the film
+// distance and the film width.  The kernels get them from the host once per launch (camera_frame_constants) instead of
+// one tanf and one W/H division per ray; same expressions, same order.
+struct CameraFrame { float dist, film_w; };
+WPT_HD CameraFrame camera_frame_constants(const wpt_camera &c, int W, int H)
+{
+    CameraFrame f;
+    f.dist = c.film_size_y * 0.5f / tanf(c.fov_y * 0.5f);
+    const float ratio = (float)W / (float)H;
+    f.film_w = ratio * c.film_size_y;
+    return f;
+}
+
+WPT_HD void camera_ray(const wpt_camera &c, const CameraFrame &cf, int px, int py, int W, int H, const float xi[4], V3 &org, V3 &dir)
 {
     // sample_pos: lens point in the local x-z plane (sic), pinhole.h:27-32
     float lx = 0.0f, lz = 0.0f;
@@ -121,11 +134,10 @@ WPT_HD void camera_ray(const wpt_camera &c, int px, int py, int W, int H, const 
     const V3 lens_local = v3(fmaf(c.x[2], rel.z, fmaf(c.x[1], rel.y, c.x[0] * rel.x)),
                              fmaf(c.y[2], rel.z, fmaf(c.y[1], rel.y, c.y[0] * rel.x)),
                              fmaf(c.z[2], rel.z, fmaf(c.z[1], rel.y, c.z[0] * rel.x)));
-    const float dist = c.film_size_y * 0.5f / tanf(c.fov_y * 0.5f);
-    const float ratio = (float)W / (float)H;
+    const float dist = cf.dist;
     const float ndc_x = ((float)px + xi[2]) / (float)W;
     const float ndc_y = ((float)py + xi[3]) / (float)H;
-    const float fx = (0.5f - ndc_x) * (ratio * c.film_size_y);
+    const float fx = (0.5f - ndc_x) * cf.film_w;
     const float fy = (0.5f - ndc_y) * c.film_size_y;
     const V3 focal = v3(c.focal_dist * fx / dist, c.focal_dist * fy / dist, c.focal_dist * dist / dist);
     const V3 d = normalize3(v3(focal.x - lens_local.x, focal.y - lens_local.y, focal.z - lens_local.z));

@@ -34,7 +34,9 @@ def _worker(rank, world, port, q):
     # unsharded pre-pass, the sharded one must still be entered by both (it is a collective)
     # with three or more ranks also a 3 x 2 image: ceil(6 / 4) = 2 pixels per rank leaves the last rank of four without
     # a single pixel of the pre-pass — it must launch nothing and still join the all-gather
-    cases = [(0, 24, W, H), (1, 24, W, H), (1, 15, W, H)] + ([(1, 16, 3, 2)] if world >= 3 else [])
+    # (at least 8 samples per rank in the first two, or the unsharded pre-pass would not run and the retrace counts
+    # could not be compared; 8 * world - 1 samples split 8, ..., 8, 7)
+    cases = [(0, 12 * world, W, H), (1, 12 * world, W, H), (1, 8 * world - 1, W, H)] + ([(1, 16, 3, 2)] if world >= 3 else [])
     for shard, spp, W, H in cases:
         r = wpt.Renderer(scene, W, H, 8)
         if shard:
