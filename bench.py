@@ -357,16 +357,31 @@ def run_ours(args):
     host_film = pinned.array
     e_steps = max(1, args.steps)           # the same number of frames as the device-timed loop
 
+    shared = None
+    if world > 1 and args.e2e_scatter:
+        # N > 1: no root.  ncclReduceScatter leaves 1/N of the summed film on every rank; each scales its slice and DMAs
+        # it to its place in ONE host film that all ranks map (a /dev/shm file, page-locked in every process)
+        pad, _, _ = reducer.shard_layout(N)
+        film_rs = torch.zeros(pad, device="cuda")
+        film_rs_planes = film_rs[:3 * N].view(3, N)
+        shared = wdist.SharedHostFilm(os.path.dirname(cache), 3 * N, rank, dist.barrier)
+
     def e2e_step():
         if world == 1:
             _, st = r.render_host(cam, spp_begin, spp, depth, seed=SEED, out=host_film)     # wpt_render_host
             return st
-        film.zero_()
-        r.render(cam, film, spp_begin, spp, depth, seed=SEED)
-        reducer.reduce(film, 0)
-        if rank == 0:
-            wpt.film_scale(film, 1.0 / spp_total)
-            torch.from_numpy(host_film).copy_(film, non_blocking=True)      # pinned destination: plain DMA
+        if shared is None:
+            film.zero_()
+            r.render(cam, film, spp_begin, spp, depth, seed=SEED)
+            reducer.reduce(film, 0)
+            if rank == 0:
+                wpt.film_scale(film, 1.0 / spp_total)
+                torch.from_numpy(host_film).copy_(film, non_blocking=True)      # pinned destination: plain DMA
+            return r.finish()                                                 # synchronises the stream
+        film_rs.zero_()
+        r.render(cam, film_rs_planes, spp_begin, spp, depth, seed=SEED)
+        reducer.reduce_scatter(film_rs, N)                                    # wpt_film_reduce_scatter
+        reducer.shard_finish(film_rs, N, 1.0 / spp_total, shared.array)       # own slice: 1/spp + D2H into the shared film
         return r.finish()                                                     # synchronises the stream
 
     e2e_step()
@@ -392,7 +407,10 @@ def run_ours(args):
            "what": ("wpt_render_host: host camera/config in, film zero + full frame + 1/spp + D2H of the planar film "
                     "into pinned host memory" if world == 1 else
                     "per rank: film zero + this rank's samples; wpt_film_reduce onto rank 0; rank 0: 1/spp + D2H of the "
-                    "reduced film into pinned host memory; host clock, max over ranks")}
+                    "reduced film into pinned host memory; host clock, max over ranks" if shared is None else
+                    "per rank: film zero + this rank's samples; wpt_film_reduce_scatter (no root); every rank: 1/spp on its "
+                    "1/N of the film + D2H of that slice into ONE host film shared by the ranks (/dev/shm mapping, page-locked "
+                    "in every process); d2h bytes are the sum over the ranks; host clock, max over ranks")}
 
     # ---- sameness across N: the UN-normalised frame, reduced onto rank 0, summed per channel on the host in fp64.
     # Every contribution of an all-white scene is exactly 1.0 and a pixel holds at most spp of them, so the film is
@@ -416,6 +434,11 @@ def run_ours(args):
                     "segments": int(cseg.item()),
                     "what": "per-channel sums of the un-normalised reduced film (fp64 on the host) of one untimed frame; "
                             "`exact`: every pixel an integer (all-white scene), so the sums are too"}
+        if shared is not None:
+            # the host film the end-to-end leg assembled from the ranks' slices against the film reduced onto rank 0
+            eh = shared.array.reshape(3, N).astype(np.float64) * spp_total
+            checksum["e2e_film_checksum"] = [int(round(x)) for x in eh.sum(axis=1)]
+            checksum["e2e_film_equals_reduced"] = bool(np.allclose(eh, hf, rtol=1e-6, atol=1e-6 * spp_total))
 
     # ---- roofline of the dominant kernel (trace), measured live with CUDA events per kernel
     roof = None
@@ -495,6 +518,8 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
+        if shared is not None:
+            shared.close()
         if rank == 0 and cache:
             shutil.rmtree(os.path.dirname(cache), ignore_errors=True)
         reducer.close()
@@ -521,6 +546,9 @@ def main():
     ap.add_argument("--graph", action="store_true", help="replay the frame from a CUDA graph (single GPU)")
     ap.add_argument("--seeding", type=int, default=1, help="1 = depth seeding of the camera rays (default), 0 = off")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-scatter", type=int, default=0,
+                    help="N>1 end-to-end leg: 1 = wpt_film_reduce_scatter + every rank copies its slice into one shared host film; "
+                         "0 = wpt_film_reduce onto rank 0 + D2H there (default)")
     ap.add_argument("--ref-spp", type=int, default=0, help="--impl reference: samples per step (0 = the workload's, like the GPU arm)")
     ap.add_argument("--quick", action="store_true", help="profiling runs: timed loop only, short warm-up allowed")
     args = ap.parse_args()

@@ -95,7 +95,10 @@ int  wpt_scene_commit_lbvh(wpt_scene *s, int device);
  * positions and indices, library version) it is loaded instead of built, otherwise the tree is built and the file written
  * (atomically: temp file + rename).  For the G ranks of a multi-GPU job on one box (one process per GPU, same mesh): one
  * rank commits first, the others then load — one SAH build (C4: 3.5-4.7 s) instead of G.  *from_cache (optional) = 1 if
- * the tree was loaded.  A cache that cannot be read or written is not an error: the tree is built. */
+ * the tree was loaded.  A cache that cannot be read or written is not an error: the tree is built.  The file is outside
+ * input and is treated as such: besides the mesh hash it must carry this build's block layout and builder revision, a
+ * payload checksum, a depth the traversal stack holds, a level table that partitions the nodes, child runs inside the
+ * buffer and face indices inside the mesh — anything else is ignored and rebuilt.  It is written with mode 0600. */
 int  wpt_scene_commit_cached(wpt_scene *s, int device, const char *cache_path, int *from_cache);
 int  wpt_scene_stats(const wpt_scene *s, wpt_bvh_stats *out);
 /* Moved vertices, same topology: bottom-up refit of the node boxes and rewrite of the triangle blocks ON THE
@@ -158,7 +161,9 @@ typedef struct {
  * Equal-t hits (shared edges) resolve to the LOWEST primitive index, whatever the order of the tests. */
 int wpt_intersect(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
                   uint32_t n, const wpt_hit_streams *hits, void *stream);
-/* Same, HOST buffers in and out (copies inside; synchronous). */
+/* Same, HOST buffers in and out (copies inside; synchronous).  A convenience for tests and one-off queries: it allocates
+ * and frees its device staging on every call (cudaMalloc / cudaFree wait for the whole device).  A host that calls once
+ * per bounce keeps its rays on the device and uses wpt_intersect, or uses wpt_intersect_host_static below. */
 int wpt_intersect_host(const wpt_scene *s, const wpt_ray_streams *rays, const uint8_t *mask, uint32_t mask_size,
                        uint32_t n, const wpt_hit_streams *hits);
 
@@ -330,6 +335,23 @@ int  wpt_nccl_group_start(void);
 int  wpt_nccl_group_end(void);
 int  wpt_film_reduce(void *nccl_comm, float *film_r, float *film_g, float *film_b, uint32_t n, int root, void *stream);
 
+/* The same exchange without a root (no counterpart in the reference either): ncclReduceScatter leaves on rank g the
+ * sum of floats [first, first + count) of the FLATTENED planar film (r plane, then g, then b: 3n floats), in place, where
+ * wpt_film_shard_layout(n, g, n_ranks, &padded, &first, &count) says which.  `film` must be one device buffer of at least
+ * `padded` floats (3n rounded up to a multiple of n_ranks; the padding is summed too, zero it once).  Afterwards the rest
+ * of the buffer is undefined.  wpt_film_shard_finish then multiplies this rank's slice by `scale` (the 1/spp of
+ * src/main.cpp:429) and, if host_film != NULL, queues the copy of the slice to host_film + first — host_film is the
+ * WHOLE film of 3n floats; when it is one pinned buffer shared by the ranks (one process: wpt_host_alloc; one process per
+ * GPU: a shared mapping that every rank passes to wpt_host_register) the n_ranks copies run in parallel and assemble the
+ * frame on the host.  Each rank moves and copies 1/n_ranks of what the root of wpt_film_reduce does.  All asynchronous
+ * on `stream`. */
+int  wpt_film_shard_layout(uint32_t n, int rank, int n_ranks, uint64_t *padded_floats, uint64_t *first, uint64_t *count);
+int  wpt_film_reduce_scatter(void *nccl_comm, float *film, uint32_t n, int rank, int n_ranks, void *stream);
+int  wpt_film_shard_finish(float *film, uint32_t n, int rank, int n_ranks, float scale, float *host_film, void *stream);
+/* page-locks an existing host range for DMA (cudaHostRegister, portable), e.g. a shared-memory mapping of the film */
+int  wpt_host_register(void *p, size_t bytes);
+void wpt_host_unregister(void *p);
+
 /* ------------------------------------------------------------------ per-function device entry points
  * (parity tests of the fused kernels' pieces against the oracle; all DEVICE buffers) */
 /* camera rays for pixels [0,W*H) of one global sample index: o,d as 6 planar streams */
@@ -347,6 +369,19 @@ int wpt_philox(uint32_t n, uint32_t c1, uint32_t c2, uint64_t key, uint32_t *out
  * PFM: "PF\nW H\n-1\n", rows bottom-up, interleaved RGB float32 LE.  HOST planar inputs. */
 int wpt_save_pfm(const char *path, const float *r, const float *g, const float *b, uint32_t width,
                  uint32_t height);
+
+/* ------------------------------------------------------------------ checkpoint / resume
+ * No counterpart in the reference, whose film lives on the device until main() ends (src/main.cpp:434-442).  A frame is
+ * a sum over samples and the RNG is keyed on the global sample index, so the UN-normalised film plus the number of samples
+ * in it is a complete checkpoint: wpt_film_save writes HOST planar r, g, b (f32[width*height] each, before the 1/spp of
+ * src/main.cpp:429), spp_done and the seed to one file, atomically (temp file + rename) and with a checksum; a later
+ * process loads it (wpt_film_load: dimensions must match, WPT_E_IO for a truncated or damaged file), uploads the planes
+ * and goes on with wpt_render(spp_begin = spp_done, same seed) into them.  wpt_film_info reads the header only. */
+int wpt_film_save(const char *path, const float *r, const float *g, const float *b, uint32_t width, uint32_t height,
+                  uint64_t spp_done, uint64_t seed);
+int wpt_film_info(const char *path, uint32_t *width, uint32_t *height, uint64_t *spp_done, uint64_t *seed);
+int wpt_film_load(const char *path, float *r, float *g, float *b, uint32_t width, uint32_t height, uint64_t *spp_done,
+                  uint64_t *seed);
 
 #ifdef __cplusplus
 }

@@ -810,6 +810,7 @@ struct NcclApi {
     decltype(&ncclCommInitAll) CommInitAll = nullptr;
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
     decltype(&ncclReduce) Reduce = nullptr;
+    decltype(&ncclReduceScatter) ReduceScatter = nullptr;
     decltype(&ncclAllGather) AllGather = nullptr;
     decltype(&ncclGroupStart) GroupStart = nullptr;
     decltype(&ncclGroupEnd) GroupEnd = nullptr;
@@ -832,10 +833,11 @@ static int nccl_load()
     g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(sym("ncclCommDestroy"));
     g_nccl.Reduce = reinterpret_cast<decltype(g_nccl.Reduce)>(sym("ncclReduce"));
     g_nccl.AllGather = reinterpret_cast<decltype(g_nccl.AllGather)>(sym("ncclAllGather"));
+    g_nccl.ReduceScatter = reinterpret_cast<decltype(g_nccl.ReduceScatter)>(sym("ncclReduceScatter"));
     g_nccl.GroupStart = reinterpret_cast<decltype(g_nccl.GroupStart)>(sym("ncclGroupStart"));
     g_nccl.GroupEnd = reinterpret_cast<decltype(g_nccl.GroupEnd)>(sym("ncclGroupEnd"));
     g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(sym("ncclGetErrorString"));
-    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce || !g_nccl.AllGather ||
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce || !g_nccl.AllGather || !g_nccl.ReduceScatter ||
         !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.GetErrorString)
         return fail(WPT_E_STATE, "NCCL library lacks a required symbol");
     g_nccl.lib = h;
@@ -1430,6 +1432,54 @@ extern "C" int wpt_film_reduce(void *nccl_comm, float *film_r, float *film_g, fl
     return WPT_OK;
 }
 
+// The same exchange with the result left where it was computed: after ncclReduceScatter rank g holds the sum of floats
+// [g*chunk, (g+1)*chunk) of the flattened film, in place.  No rank is special, each moves 1/n of what the root of
+// wpt_film_reduce receives, and the 1/spp scale and the copy to the host that follow (wpt_film_shard_finish) touch
+// 1/n of the film per rank instead of all of it on one.
+extern "C" int wpt_film_shard_layout(uint32_t n, int rank, int n_ranks, uint64_t *padded_floats, uint64_t *first, uint64_t *count)
+{
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_film_shard_layout: bad rank");
+    const uint64_t total = 3ull * n, chunk = (total + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+    const uint64_t lo = std::min(total, (uint64_t)rank * chunk), hi = std::min(total, lo + chunk);
+    if (padded_floats) *padded_floats = chunk * (uint64_t)n_ranks;
+    if (first) *first = lo;
+    if (count) *count = hi - lo;
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_reduce_scatter(void *nccl_comm, float *film, uint32_t n, int rank, int n_ranks, void *stream)
+{
+    if (!nccl_comm || !film) return fail(WPT_E_INVALID, "wpt_film_reduce_scatter: null argument");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(WPT_E_INVALID, "wpt_film_reduce_scatter: bad rank");
+    if (int rc = nccl_load()) return rc;
+    const uint64_t chunk = (3ull * n + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+    // in place: NCCL takes recvbuff == sendbuff + rank * recvcount as the in-place form
+    WPT_NCCL(g_nccl.ReduceScatter(film, film + (size_t)rank * chunk, chunk, ncclFloat32, ncclSum,
+                                  reinterpret_cast<ncclComm_t>(nccl_comm), (cudaStream_t)stream));
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_shard_finish(float *film, uint32_t n, int rank, int n_ranks, float scale, float *host_film, void *stream)
+{
+    if (!film) return fail(WPT_E_INVALID, "wpt_film_shard_finish: null film");
+    uint64_t lo = 0, cnt = 0;
+    if (int rc = wpt_film_shard_layout(n, rank, n_ranks, nullptr, &lo, &cnt)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    launch_film_scale_flat(film + lo, (uint32_t)cnt, scale, st);
+    WPT_CUDA(cudaGetLastError());
+    if (host_film && cnt)
+        WPT_CUDA(cudaMemcpyAsync(host_film + lo, film + lo, cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    return WPT_OK;
+}
+
+extern "C" int wpt_host_register(void *p, size_t bytes)
+{
+    if (!p || !bytes) return fail(WPT_E_INVALID, "wpt_host_register: null argument");
+    WPT_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return WPT_OK;
+}
+extern "C" void wpt_host_unregister(void *p) { if (p) cudaHostUnregister(p); }
+
 // ------------------------------------------------------------------------------------------------
 // derived hit attributes (src/accel/optix_backend.h:463-486, src/main.cpp:325)
 extern "C" int wpt_scene_set_texcoords(wpt_scene *s, const float *uvs, const int32_t *uv_triplets, uint32_t n_uvs)
@@ -1512,5 +1562,92 @@ extern "C" int wpt_save_pfm(const char *path, const float *r, const float *g, co
         }
     }
     std::fclose(f);
+    return WPT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// checkpoint of a render in progress: the UN-normalised film and how many samples it holds.  The reference
+// keeps the film on the device until the end (src/main.cpp:434-442) and cannot resume; here a frame is additive over
+// [spp_begin, spp_begin + spp_count) and the RNG is keyed on the global sample index, so "film so far + spp_done + seed"
+// is all a later process needs to continue with spp_begin = spp_done.
+namespace {
+struct FilmFileHeader {
+    uint64_t magic;
+    uint32_t width, height;
+    uint64_t spp_done, seed;
+};
+constexpr uint64_t kFilmMagic = 0x314d4c4946545057ull;   // "WPTFILM1"
+int film_read_header(FILE *f, FilmFileHeader &h, const char *path)
+{
+    if (std::fread(&h, sizeof h, 1, f) != 1 || h.magic != kFilmMagic || h.width == 0 || h.height == 0)
+        return fail(WPT_E_IO, std::string("wpt_film_load: not a film checkpoint: ") + path);
+    return WPT_OK;
+}
+}  // namespace
+
+extern "C" int wpt_film_save(const char *path, const float *r, const float *g, const float *b, uint32_t width, uint32_t height,
+                             uint64_t spp_done, uint64_t seed)
+{
+    if (!path || !r || !g || !b || width == 0 || height == 0) return fail(WPT_E_INVALID, "wpt_film_save: null argument");
+    const size_t n = (size_t)width * height;
+    const std::string tmp = std::string(path) + ".tmp" + std::to_string((long)getpid());
+    FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return fail(WPT_E_IO, std::string("wpt_film_save: cannot open ") + tmp);
+    const FilmFileHeader h{kFilmMagic, width, height, spp_done, seed};
+    uint64_t sum = fnv1a_words(&h, sizeof h, 0xcbf29ce484222325ull);
+    sum = fnv1a_words(r, n * sizeof(float), sum);
+    sum = fnv1a_words(g, n * sizeof(float), sum);
+    sum = fnv1a_words(b, n * sizeof(float), sum);
+    const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(r, sizeof(float), n, f) == n &&
+                    std::fwrite(g, sizeof(float), n, f) == n && std::fwrite(b, sizeof(float), n, f) == n &&
+                    std::fwrite(&sum, sizeof sum, 1, f) == 1;
+    const bool closed = std::fclose(f) == 0;
+    // a reader sees the previous checkpoint or this one, never half of it
+    if (!ok || !closed || std::rename(tmp.c_str(), path) != 0) {
+        std::remove(tmp.c_str());
+        return fail(WPT_E_IO, std::string("wpt_film_save: cannot write ") + path);
+    }
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_info(const char *path, uint32_t *width, uint32_t *height, uint64_t *spp_done, uint64_t *seed)
+{
+    if (!path) return fail(WPT_E_INVALID, "wpt_film_info: null path");
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return fail(WPT_E_IO, std::string("wpt_film_info: cannot open ") + path);
+    FilmFileHeader h;
+    const int rc = film_read_header(f, h, path);
+    std::fclose(f);
+    if (rc) return rc;
+    if (width) *width = h.width;
+    if (height) *height = h.height;
+    if (spp_done) *spp_done = h.spp_done;
+    if (seed) *seed = h.seed;
+    return WPT_OK;
+}
+
+extern "C" int wpt_film_load(const char *path, float *r, float *g, float *b, uint32_t width, uint32_t height, uint64_t *spp_done,
+                             uint64_t *seed)
+{
+    if (!path || !r || !g || !b) return fail(WPT_E_INVALID, "wpt_film_load: null argument");
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return fail(WPT_E_IO, std::string("wpt_film_load: cannot open ") + path);
+    FilmFileHeader h;
+    if (int rc = film_read_header(f, h, path)) { std::fclose(f); return rc; }
+    if (h.width != width || h.height != height) {
+        std::fclose(f);
+        return fail(WPT_E_INVALID, "wpt_film_load: the checkpoint is " + std::to_string(h.width) + "x" + std::to_string(h.height) +
+                                       ", the film given " + std::to_string(width) + "x" + std::to_string(height));
+    }
+    const size_t n = (size_t)width * height;
+    uint64_t stored = 0;
+    const bool ok = std::fread(r, sizeof(float), n, f) == n && std::fread(g, sizeof(float), n, f) == n &&
+                    std::fread(b, sizeof(float), n, f) == n && std::fread(&stored, sizeof stored, 1, f) == 1;
+    std::fclose(f);
+    uint64_t sum = fnv1a_words(&h, sizeof h, 0xcbf29ce484222325ull);
+    if (ok) { sum = fnv1a_words(r, n * sizeof(float), sum); sum = fnv1a_words(g, n * sizeof(float), sum); sum = fnv1a_words(b, n * sizeof(float), sum); }
+    if (!ok || sum != stored) return fail(WPT_E_IO, std::string("wpt_film_load: truncated or damaged checkpoint: ") + path);
+    if (spp_done) *spp_done = h.spp_done;
+    if (seed) *seed = h.seed;
     return WPT_OK;
 }

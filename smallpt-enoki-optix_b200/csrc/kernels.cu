@@ -417,6 +417,19 @@ void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cu
     if (n) film_scale_kernel<<<blocks, 256, 0, st>>>(r, g, b, n, scale);
 }
 
+// one contiguous run of film floats (a rank's slice after wpt_film_reduce_scatter)
+__global__ void film_scale_flat_kernel(float *p, uint32_t n, float scale)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] *= scale;
+}
+void launch_film_scale_flat(float *p, uint32_t n, float scale, cudaStream_t st)
+{
+    uint32_t blocks = (n + 255) / 256;
+    const uint32_t cap = (uint32_t)device_sms() * 8u;
+    if (blocks > cap) blocks = cap;
+    if (n) film_scale_flat_kernel<<<blocks, 256, 0, st>>>(p, n, scale);
+}
+
 __global__ void philox_kernel(uint32_t n, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1, uint32_t *out)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

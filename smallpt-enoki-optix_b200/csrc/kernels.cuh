@@ -107,6 +107,7 @@ void launch_shade_streams(uint32_t n, const float *const o[3], const float *cons
                           const float4 *tri_attr, const float *albedo, float *const no[3], float *const nd[3],
                           float *const w[3], cudaStream_t st, const TexArgs *tex = nullptr);
 void launch_film_scale(float *r, float *g, float *b, uint32_t n, float scale, cudaStream_t st);
+void launch_film_scale_flat(float *p, uint32_t n, float scale, cudaStream_t st);
 void launch_refit(Block64 *blocks, const uint32_t *level_nodes, const uint32_t *level_begin_host, uint32_t n_levels,
                   const float *pos, const int32_t *pidx, float *boxes, TriAttr48 *attr, const uint8_t *geo_normal,
                   cudaStream_t st, uint32_t *bad_flag = nullptr);

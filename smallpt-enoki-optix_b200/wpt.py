@@ -92,6 +92,12 @@ def lib():
         L.wpt_obj_material_name.argtypes = [C.c_void_p, C.c_uint32]
         L.wpt_host_alloc.argtypes = [C.c_size_t, C.c_void_p]
         L.wpt_host_free.argtypes = [C.c_void_p]
+        L.wpt_host_register.argtypes = [C.c_void_p, C.c_size_t]
+        L.wpt_host_unregister.argtypes = [C.c_void_p]
+        L.wpt_host_unregister.restype = None
+        L.wpt_film_shard_layout.argtypes = [C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.wpt_film_reduce_scatter.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p]
+        L.wpt_film_shard_finish.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
         L.wpt_nccl_comm_destroy.argtypes = [C.c_void_p]
         L.wpt_film_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         _lib = L
@@ -534,6 +540,31 @@ class Fimage:
         r, g, b = (_np(x, np.float32).reshape(-1) for x in (r, g, b))
         _check(lib().wpt_save_pfm(str(filepath).encode(), C.c_void_p(r.ctypes.data), C.c_void_p(g.ctypes.data),
                                   C.c_void_p(b.ctypes.data), C.c_uint32(width), C.c_uint32(height)))
+
+
+def film_save(path, film, width, height, spp_done, seed=0):
+    """checkpoint of a render in progress (wpt_film_save): film = HOST un-normalised planar [3, H*W] float32"""
+    f = _np(film, np.float32).reshape(3, -1)
+    assert f.shape[1] == width * height
+    _check(lib().wpt_film_save(str(path).encode(), C.c_void_p(f[0].ctypes.data), C.c_void_p(f[1].ctypes.data),
+                               C.c_void_p(f[2].ctypes.data), C.c_uint32(width), C.c_uint32(height), C.c_uint64(spp_done),
+                               C.c_uint64(seed)))
+
+
+def film_info(path):
+    """(width, height, spp_done, seed) of a checkpoint (wpt_film_info)"""
+    w, h, n, s = C.c_uint32(), C.c_uint32(), C.c_uint64(), C.c_uint64()
+    _check(lib().wpt_film_info(str(path).encode(), C.byref(w), C.byref(h), C.byref(n), C.byref(s)))
+    return w.value, h.value, n.value, s.value
+
+
+def film_load(path, width, height):
+    """-> (film [3, H*W] float32 un-normalised, spp_done, seed) (wpt_film_load)"""
+    f = np.empty((3, width * height), np.float32)
+    n, s = C.c_uint64(), C.c_uint64()
+    _check(lib().wpt_film_load(str(path).encode(), C.c_void_p(f[0].ctypes.data), C.c_void_p(f[1].ctypes.data),
+                               C.c_void_p(f[2].ctypes.data), C.c_uint32(width), C.c_uint32(height), C.byref(n), C.byref(s)))
+    return f, n.value, s.value
 
 
 def scene_from(sd, device=0, builder="sah", cache_path=None):

@@ -66,7 +66,57 @@ class FilmReducer:
         wpt._check(self.L.wpt_film_reduce(self.comm, C.c_void_p(base), C.c_void_p(base + 4 * N), C.c_void_p(base + 8 * N),
                                           C.c_uint32(N), C.c_int(root), wpt._stream_handle(stream)))
 
+    def shard_layout(self, n_pixels):
+        """(padded_floats, first, count) of this rank's slice of the flattened [3, N] film (wpt_film_shard_layout)"""
+        import wpt
+        pad, lo, cnt = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        wpt._check(self.L.wpt_film_shard_layout(C.c_uint32(n_pixels), C.c_int(self.rank), C.c_int(self.world),
+                                                C.byref(pad), C.byref(lo), C.byref(cnt)))
+        return pad.value, lo.value, cnt.value
+
+    def reduce_scatter(self, film, n_pixels, stream=None):
+        """film: flat CUDA float32 buffer of at least shard_layout()[0] floats holding the planar [3, N] film; afterwards
+        this rank's slice holds the sum over the ranks (wpt_film_reduce_scatter: ncclReduceScatter, in place)"""
+        import wpt
+        wpt._check(self.L.wpt_film_reduce_scatter(self.comm, C.c_void_p(film.data_ptr()), C.c_uint32(n_pixels),
+                                                  C.c_int(self.rank), C.c_int(self.world), wpt._stream_handle(stream)))
+
+    def shard_finish(self, film, n_pixels, scale, host_film=None, stream=None):
+        """scale this rank's slice and queue its copy into host_film (numpy float32 over pinned / registered memory of
+        3 * N floats: the whole film, every rank writes its own part)"""
+        import wpt
+        hp = C.c_void_p(host_film.ctypes.data) if host_film is not None else None
+        wpt._check(self.L.wpt_film_shard_finish(C.c_void_p(film.data_ptr()), C.c_uint32(n_pixels), C.c_int(self.rank),
+                                                C.c_int(self.world), C.c_float(scale), hp, wpt._stream_handle(stream)))
+
     def close(self):
         if self.comm:
             self.L.wpt_nccl_comm_destroy(self.comm)
             self.comm = C.c_void_p()
+
+
+class SharedHostFilm:
+    """The host film of a frame rendered by one process per GPU: a file in `directory` (a tmpfs such as /dev/shm) mapped
+    by every rank and page-locked in each (wpt_host_register), so that every rank's slice goes to its place by DMA.
+    `array` is the flat float32 [3 * N] film.  Rank 0 creates the file; call after the ranks agreed on `directory`."""
+
+    def __init__(self, directory, n_floats, rank, barrier):
+        import os
+        import numpy as np
+        import wpt
+        self.path = os.path.join(directory, "film.f32")
+        nbytes = (4 * n_floats + 4095) // 4096 * 4096          # whole pages: that is what gets page-locked
+        if rank == 0:
+            with open(self.path, "wb") as f:
+                f.truncate(nbytes)
+        barrier()
+        self._map = np.memmap(self.path, dtype=np.float32, mode="r+", shape=(nbytes // 4,))
+        self.array = self._map[:n_floats]
+        self._ptr = C.c_void_p(self._map.ctypes.data)
+        wpt._check(wpt.lib().wpt_host_register(self._ptr, C.c_size_t(nbytes)))
+
+    def close(self):
+        import wpt
+        if self._ptr:
+            wpt.lib().wpt_host_unregister(self._ptr)
+            self._ptr = None

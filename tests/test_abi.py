@@ -72,3 +72,30 @@ def test_product_does_not_reach_the_oracle():
     import subprocess
     out = subprocess.run(["ldd", os.path.join(pkg, "libwpt.so")], capture_output=True, text=True).stdout
     assert "oracle" not in out and "embree" not in out
+
+
+def test_film_checkpoint_roundtrip_and_damage(tmp_path):
+    """wpt_film_save / wpt_film_info / wpt_film_load are host-only: round trip bit for bit, atomic replace, and a
+    truncated or altered file, or one of another size, is refused."""
+    import wpt
+    rng = np.random.default_rng(3)
+    W, H = 7, 5
+    film = rng.uniform(0, 9, (3, W * H)).astype(np.float32)
+    p = tmp_path / "frame.ckpt"
+    wpt.film_save(p, film, W, H, 37, seed=0xDEADBEEFCAFE)
+    assert wpt.film_info(p) == (W, H, 37, 0xDEADBEEFCAFE)
+    back, spp, seed = wpt.film_load(p, W, H)
+    assert spp == 37 and seed == 0xDEADBEEFCAFE and np.array_equal(back.view(np.uint32), film.view(np.uint32))
+    wpt.film_save(p, film * 2, W, H, 74)                      # replaces the file as a whole
+    assert wpt.film_info(p)[2] == 74 and not list(tmp_path.glob("*.tmp*"))
+    with pytest.raises(wpt.WptError) as e:
+        wpt.film_load(p, H, W)
+    assert e.value.code == 1 and "7x5" in str(e.value)
+    raw = p.read_bytes()
+    for bad in (raw[:-5], raw[:40] + bytes([raw[40] ^ 1]) + raw[41:], b"PF\n7 5\n-1\n" + raw[11:]):
+        p.write_bytes(bad)
+        with pytest.raises(wpt.WptError) as e:
+            wpt.film_load(p, W, H)
+        assert e.value.code == 5
+    with pytest.raises(wpt.WptError):
+        wpt.film_info(tmp_path / "absent.ckpt")

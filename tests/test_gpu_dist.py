@@ -50,6 +50,39 @@ def _worker(rank, world, port, q):
         dist.reduce(segs, dst=0)
         out.append((film, segs, spp, W, H))
         r.close()
+    # the exchange without a root: reduce-scatter, every rank scales its slice and copies it into ONE host film that all
+    # ranks map (wpt_film_reduce_scatter / wpt_film_shard_finish / wpt_host_register); 13 x 7 pixels: 273 floats do not
+    # divide by 2 or 4, so the padded tail is exercised
+    import tempfile
+    import numpy as np
+    Ws, Hs, spp_s = 13, 7, 8 * world
+    box = [tempfile.mkdtemp(prefix="wpt_test_", dir="/dev/shm") if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    shared = wpt_dist.SharedHostFilm(box[0], 3 * Ws * Hs, rank, dist.barrier)
+    pad, lo, cnt = red.shard_layout(Ws * Hs)
+    flat = torch.zeros(pad, device="cuda")
+    rs = wpt.Renderer(scene, Ws, Hs, 8)
+    b, c = wpt_dist.spp_range_strong(rank, world, spp_s)
+    rs.render(cam, flat[:3 * Ws * Hs].view(3, Ws * Hs), b, c, depth, seed=9)
+    red.reduce_scatter(flat, Ws * Hs)
+    red.shard_finish(flat, Ws * Hs, 1.0 / spp_s, shared.array)
+    rs.finish()
+    torch.cuda.synchronize()
+    dist.barrier()
+    scatter_ok = None
+    if rank == 0:
+        whole = torch.zeros(3, Ws * Hs, device="cuda")
+        rs.render(cam, whole, 0, spp_s, depth, seed=9)
+        rs.finish()
+        want = (whole / spp_s).cpu().numpy().reshape(-1)
+        scatter_ok = bool(np.allclose(np.asarray(shared.array), want, rtol=0, atol=2e-6)) and float(want.sum()) > 0 \
+            and pad % world == 0 and pad >= 3 * Ws * Hs
+    dist.barrier()
+    shared.close()
+    rs.close()
+    if rank == 0:
+        import shutil
+        shutil.rmtree(box[0], ignore_errors=True)
     if rank == 0:
         ok = []
         for f, s, spp, W, H in out:
@@ -59,7 +92,7 @@ def _worker(rank, world, port, q):
             st = r.finish()
             ok.append(bool(torch.allclose(f, whole, rtol=0, atol=2e-5)) and int(s[0]) == st["segments"])
         # sharded and unsharded pre-pass give the same seeds: the same rays are traced a second time
-        q.put((ok, int(out[0][1][1]) == int(out[1][1][1]), float(whole.sum()) > 0))
+        q.put((ok, int(out[0][1][1]) == int(out[1][1][1]), float(whole.sum()) > 0 and scatter_ok))
     red.close()
     dist.destroy_process_group()
 

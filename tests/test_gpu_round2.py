@@ -536,3 +536,73 @@ def test_pinned_film_outlives_the_objects_that_made_it():
     del r, live, again
     gc.collect()
     assert np.array_equal(keep, want)
+
+
+def test_render_resumes_from_a_film_checkpoint(tmp_path):
+    """SURVEY §5 checkpoint/resume: samples 0..5, save, a NEW renderer loads and renders 5..8 on top == samples 0..8 in
+    one go — bit for bit here, because every contribution of an all-white scene is exactly 1.0"""
+    import torch
+    import wpt
+    sd = scenes.cornell(16)
+    scene = wpt.scene_from(sd)
+    cam = wpt.camera_from(sd)
+    W, H, depth, seed = 96, 64, 5, 77
+    whole = torch.zeros(3, W * H, device="cuda")
+    r = wpt.Renderer(scene, W, H, 4)
+    r.render(cam, whole, 0, 8, depth, seed=seed)
+    r.finish()
+    part = torch.zeros(3, W * H, device="cuda")
+    r.render(cam, part, 0, 5, depth, seed=seed)
+    r.finish()
+    r.close()
+    wpt.film_save(tmp_path / "f.ckpt", part.cpu().numpy(), W, H, 5, seed)
+    del part
+    w, h, done, sd_seed = wpt.film_info(tmp_path / "f.ckpt")
+    host, done2, _ = wpt.film_load(tmp_path / "f.ckpt", w, h)
+    assert (w, h, done, sd_seed, done2) == (W, H, 5, seed, 5)
+    cont = torch.from_numpy(host).cuda()
+    r2 = wpt.Renderer(wpt.scene_from(sd), W, H, 4)
+    r2.render(cam, cont, done, 8 - done, depth, seed=sd_seed)
+    r2.finish()
+    assert torch.equal(cont, whole) and float(whole.sum()) > 0
+
+
+def test_reduce_scatter_entry_points_on_a_one_rank_communicator(tmp_path):
+    """wpt_film_shard_layout / wpt_film_reduce_scatter / wpt_film_shard_finish / wpt_host_register on ONE GPU (a
+    communicator of one rank: the collective is the identity): symbol binding, slice arithmetic, the scale kernel on a
+    slice and the DMA into a page-locked file mapping.  The N-rank sum is tests/test_gpu_dist.py's business."""
+    import ctypes as C
+    import torch
+    import wpt
+    L = wpt.lib()
+    # slice arithmetic, no device needed: 3 * 91 = 273 floats over 4 ranks -> 69, 69, 69, 66; padded to 276
+    got = []
+    for g in range(4):
+        pad, lo, cnt = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        assert L.wpt_film_shard_layout(C.c_uint32(91), C.c_int(g), C.c_int(4), C.byref(pad), C.byref(lo), C.byref(cnt)) == 0
+        got.append((pad.value, lo.value, cnt.value))
+    assert got == [(276, 0, 69), (276, 69, 69), (276, 138, 69), (276, 207, 66)]
+    assert L.wpt_film_shard_layout(C.c_uint32(91), C.c_int(4), C.c_int(4), None, None, None) == 1
+    idb = (C.c_char * 128)()
+    wpt._check(L.wpt_nccl_unique_id(idb))
+    comm = C.c_void_p()
+    wpt._check(L.wpt_nccl_comm_create(C.c_char_p(idb.raw), C.c_int(1), C.c_int(0), C.c_int(0), C.byref(comm)))
+    n = 91
+    film = torch.arange(3 * n, dtype=torch.float32, device="cuda") + 1.0
+    want = (film * 0.25).cpu().numpy()
+    import shutil
+    import tempfile
+    import wpt_dist
+    box = tempfile.mkdtemp(prefix="wpt_test_", dir="/dev/shm")     # a tmpfs: file mappings of a disk cannot be page-locked
+    shared = wpt_dist.SharedHostFilm(box, 3 * n, 0, lambda: None)
+    host = shared.array
+    try:
+        wpt._check(L.wpt_film_reduce_scatter(comm, C.c_void_p(film.data_ptr()), C.c_uint32(n), C.c_int(0), C.c_int(1), None))
+        wpt._check(L.wpt_film_shard_finish(C.c_void_p(film.data_ptr()), C.c_uint32(n), C.c_int(0), C.c_int(1), C.c_float(0.25),
+                                           C.c_void_p(host.ctypes.data), None))
+        torch.cuda.synchronize()
+        assert np.array_equal(np.asarray(host), want) and np.array_equal(film.cpu().numpy(), want)
+    finally:
+        shared.close()
+        shutil.rmtree(box, ignore_errors=True)
+        L.wpt_nccl_comm_destroy(comm)
